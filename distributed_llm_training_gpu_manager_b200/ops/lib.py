@@ -34,6 +34,22 @@ _SIGNATURES = {
     "bz_version": (i32, []),
     "bz_sm_count": (i32, []),
     "bz_gemm_bf16": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "bz_rmsnorm_fwd": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, f32, vp]),
+    "bz_rmsnorm_bwd_workspace_floats": (i32, [i32, i32]),
+    "bz_rmsnorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, vp, i32, i32, f32, vp]),
+    "bz_rope": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
+    "bz_swiglu_fwd": (i32, [vp, vp, i64, i32, vp]),
+    "bz_swiglu_bwd": (i32, [vp, vp, vp, i64, i32, vp]),
+    "bz_embedding_fwd": (i32, [vp, i32, vp, vp, i64, i32, i32, vp]),
+    "bz_embedding_bwd": (i32, [vp, i32, vp, vp, i32, i64, i32, i32, vp]),
+    "bz_cross_entropy": (i32, [vp, vp, i32, vp, vp, i32, i32, i64, f32, i32, vp]),
+    "bz_add_bf16": (i32, [vp, vp, vp, i64, vp]),
+    "bz_adamw": (i32, [vp, vp, vp, vp, i32, vp, i64, f32, f32, f32, f32, f32, i32, f32, vp, vp, vp]),
+    "bz_sumsq_workspace_floats": (i32, []),
+    "bz_sumsq": (i32, [vp, i32, i64, vp, vp, i32, vp, vp]),
+    "bz_clip_coef": (i32, [vp, f32, f32, vp, vp, vp, vp]),
+    "bz_cast_f32_to_bf16": (i32, [vp, vp, i64, vp]),
+    "bz_cast_bf16_to_f32": (i32, [vp, vp, i64, vp]),
 }
 
 

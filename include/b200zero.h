@@ -41,6 +41,64 @@ int bz_sm_count(void);
 int bz_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                  int a_mn_major, int b_mn_major, int out_mode, int cta_group, int max_ctas, void* stream);
 
+/* ---- K5: RMSNorm (optionally fused with the preceding residual add) ------
+ * fwd: xo = x + delta (only when delta != NULL; written to x_out), y = xo*rstd*w.
+ *      rstd (fp32 [T]) may be NULL. bf16 tensors, D % 8 == 0, D <= 8192.
+ * bwd: dx = dres + d(rmsnorm)/dx ; dw (+)= sum over rows. `workspace` must hold
+ *      bz_rmsnorm_bwd_workspace_floats(T, D) floats when dw != NULL. rstd may be
+ *      NULL (recomputed). Replaces torch-eager RMSNorm. */
+int bz_rmsnorm_fwd(const void* x, const void* delta, const void* w, void* x_out, void* y, float* rstd, int T,
+                   int D, float eps, void* stream);
+int bz_rmsnorm_bwd_workspace_floats(int T, int D);
+int bz_rmsnorm_bwd(const void* x, const void* w, const float* rstd, const void* dy, const void* dres, void* dx,
+                   void* dw, int dw_is_f32, int dw_accumulate, float* workspace, int T, int D, float eps,
+                   void* stream);
+
+/* ---- K7: RoPE, in place on the first n_rot_heads heads of each row --------
+ * cos/sin: fp32 [S, head_dim/2]; position = row % S; inverse=1 applies the
+ * transpose rotation (backward). */
+int bz_rope(void* buf, const float* cos_t, const float* sin_t, int T, int S, int n_rot_heads, int head_dim, int ld,
+            int inverse, void* stream);
+
+/* ---- K8: SwiGLU on a fused [T, 2F] gate|up buffer ---- */
+int bz_swiglu_fwd(const void* gate_up, void* act, long long T, int F, void* stream);
+int bz_swiglu_bwd(const void* gate_up, const void* dact, void* dgate_up, long long T, int F, void* stream);
+
+/* ---- K10: embedding gather / scatter-add ------------ */
+int bz_embedding_fwd(const void* ids, int ids_are_i64, const void* table, void* out, long long T, int D, int V,
+                     void* stream);
+int bz_embedding_bwd(const void* ids, int ids_are_i64, const void* dout, void* dtable, int dtable_is_f32,
+                     long long T, int D, int V, void* stream);
+
+/* ---- K9 (part): cross-entropy fwd+bwd on a logits chunk -------------------
+ * loss[t] = lse(z_t) - z_t[y_t]; when write_grad, logits are overwritten by
+ * (softmax - onehot) * grad_scale. targets < 0 are ignored. V % 8 == 0.
+ *  */
+int bz_cross_entropy(void* logits, const void* targets, int targets_are_i64, float* loss, float* lse, int T, int V,
+                     long long ld, float grad_scale, int write_grad, void* stream);
+
+int bz_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
+
+/* ---- K11 / F9 / F10: optimizer-side kernels --------------------------------
+ * bz_adamw: torch.optim.AdamW semantics on flat fp32 master/m/v; grad bf16 or
+ *   fp32, multiplied by grad_scale * (*grad_scale_dev if non-NULL); writes the
+ *   bf16 copy of the updated weights when param_bf16 != NULL; does nothing when
+ *   *skip_flag != 0 (non-finite step). `step` is 1-based.
+ * bz_sumsq: out (+)= sum(g^2); sets *nonfinite_flag when the sum is not finite.
+ *   `workspace` must hold bz_sumsq_workspace_floats() floats.
+ * bz_clip_coef: coef = min(1, max_norm/(sqrt(sumsq)+1e-6)) * extra_scale on device.
+ * (DeepSpeed FusedAdam / grad-norm path: SURVEY.md §2.3 F7, F9, F10) */
+int bz_adamw(float* master, float* m, float* v, const void* grad, int grad_is_f32, void* param_bf16, long long n,
+             float lr, float beta1, float beta2, float eps, float weight_decay, int step, float grad_scale,
+             const float* grad_scale_dev, const int* skip_flag, void* stream);
+int bz_sumsq_workspace_floats(void);
+int bz_sumsq(const void* g, int g_is_f32, long long n, float* workspace, float* out, int accumulate,
+             int* nonfinite_flag, void* stream);
+int bz_clip_coef(const float* sumsq, float max_norm, float extra_scale, float* coef_out, float* norm_out,
+                 int* nonfinite_flag, void* stream);
+int bz_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
+int bz_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

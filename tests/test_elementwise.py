@@ -1,0 +1,153 @@
+"""Bandwidth-bound kernels vs their fp32 PyTorch oracles. The same tests run on CPU (oracle
+path, checks the wrappers' plumbing) and on B200 under ``-m gpu`` (native kernels)."""
+import pytest
+import torch
+
+from distributed_llm_training_gpu_manager_b200.ops import elementwise as E
+from distributed_llm_training_gpu_manager_b200.ops import optim as O
+
+DEVS = ["cpu", pytest.param("cuda", marks=pytest.mark.gpu)]
+
+
+def close(a, b, rtol=2e-2, atol=2e-2):
+    assert torch.allclose(a.float().cpu(), b.float().cpu(), rtol=rtol, atol=atol), \
+        f"max diff {(a.float().cpu() - b.float().cpu()).abs().max().item()}"
+
+
+@pytest.mark.parametrize("dev", DEVS)
+@pytest.mark.parametrize("T,D", [(37, 128), (64, 4096), (9, 8192), (300, 1600)])
+def test_rmsnorm_fwd_bwd(dev, T, D):
+    torch.manual_seed(0)
+    x = torch.randn(T, D, device=dev).bfloat16()
+    dl = torch.randn(T, D, device=dev).bfloat16()
+    w = (1 + 0.1 * torch.randn(D, device=dev)).bfloat16()
+    dy = torch.randn(T, D, device=dev).bfloat16()
+    y, rstd, xo = E.rmsnorm_fwd(x, w, 1e-5, delta=dl)
+    yr, rr, xor_ = E.rmsnorm_ref(x, w, 1e-5, dl)
+    close(y, yr); close(rstd, rr, 1e-3, 1e-3); close(xo, xor_)
+    y2, _, none = E.rmsnorm_fwd(x, w, 1e-5)
+    assert none is None
+    close(y2, E.rmsnorm_ref(x, w, 1e-5)[0])
+    # backward vs autograd on the fp32 restatement
+    xf = x.float().requires_grad_(); wf = w.float().requires_grad_()
+    out = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5) * wf
+    out.backward(dy.float())
+    dres = torch.randn(T, D, device=dev).bfloat16()
+    dx, dw = E.rmsnorm_bwd(x, w, dy, 1e-5, rstd=None, dres=dres)
+    close(dx, xf.grad + dres.float(), 3e-2, 3e-2)
+    close(dw, wf.grad, 3e-2, 0.15 * (T ** 0.5) / 4)
+    acc = torch.ones(D, device=dev, dtype=torch.float32)
+    E.rmsnorm_bwd(x, w, dy, 1e-5, dw_out=acc, dw_accumulate=True)
+    close(acc, wf.grad + 1, 3e-2, 0.15 * (T ** 0.5) / 4)
+
+
+@pytest.mark.parametrize("dev", DEVS)
+def test_rope_roundtrip_and_oracle(dev):
+    torch.manual_seed(1)
+    T, S, Hq, Hk, hd = 96, 48, 4, 2, 128
+    qkv = torch.randn(T, (Hq + 2 * Hk) * hd, device=dev).bfloat16()
+    orig = qkv.clone()
+    ref = E.rope_ref(orig.clone(), S, Hq + Hk, hd, 500000.0)
+    E.rope_(qkv, S, Hq + Hk, hd, 500000.0)
+    close(qkv, ref, 1e-2, 1e-2)
+    assert torch.equal(qkv[:, (Hq + Hk) * hd:], orig[:, (Hq + Hk) * hd:])  # V untouched
+    E.rope_(qkv, S, Hq + Hk, hd, 500000.0, inverse=True)
+    close(qkv, orig, 3e-2, 3e-2)
+
+
+@pytest.mark.parametrize("dev", DEVS)
+def test_swiglu(dev):
+    torch.manual_seed(2)
+    T, F = 50, 256
+    gu = torch.randn(T, 2 * F, device=dev).bfloat16()
+    d = torch.randn(T, F, device=dev).bfloat16()
+    guf = gu.float().requires_grad_()
+    ref = torch.nn.functional.silu(guf[:, :F]) * guf[:, F:]
+    ref.backward(d.float())
+    close(E.swiglu_fwd(gu), ref)
+    close(E.swiglu_bwd(gu, d), guf.grad, 3e-2, 3e-2)
+
+
+@pytest.mark.parametrize("dev", DEVS)
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float32])
+def test_embedding(dev, dt):
+    torch.manual_seed(3)
+    V, D, T = 1000, 128, 777
+    table = torch.randn(V, D, device=dev).bfloat16()
+    ids = torch.randint(0, V, (T,), device=dev)
+    close(E.embedding_fwd(ids, table), table[ids], 0, 0)
+    dout = torch.randn(T, D, device=dev).bfloat16()
+    dtab = torch.zeros(V, D, device=dev, dtype=dt)
+    E.embedding_bwd(ids, dout, dtab)
+    ref = torch.zeros(V, D, device=dev).index_add_(0, ids, dout.float())
+    close(dtab, ref, 3e-2, 6e-2)
+
+
+@pytest.mark.parametrize("dev", DEVS)
+def test_cross_entropy(dev):
+    torch.manual_seed(4)
+    T, V = 65, 2048
+    z = (3 * torch.randn(T, V, device=dev)).bfloat16()
+    y = torch.randint(0, V, (T,), device=dev)
+    y[5] = -100
+    zf = z.float().requires_grad_()
+    ref = torch.nn.functional.cross_entropy(zf, y, ignore_index=-100, reduction="none")
+    (ref.sum() * 0.5).backward()
+    work = z.clone()
+    loss = E.cross_entropy_(work, y, grad_scale=0.5)
+    close(loss, ref, 1e-2, 2e-2)
+    close(work, zf.grad, 5e-2, 2e-3)
+
+
+@pytest.mark.parametrize("dev", DEVS)
+@pytest.mark.parametrize("gdt", [torch.bfloat16, torch.float32])
+def test_adamw_matches_torch(dev, gdt):
+    torch.manual_seed(5)
+    n = 4099  # exercises the scalar tail
+    p0 = torch.randn(n, device=dev)
+    ref_p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.AdamW([ref_p], lr=1e-2, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01)
+    master, m, v = p0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    pout = torch.empty(n, device=dev, dtype=torch.bfloat16)
+    for step in range(1, 4):
+        g = torch.randn(n, device=dev).to(gdt)
+        ref_p.grad = g.float().clone()
+        opt.step()
+        O.adamw_step(master, m, v, g, lr=1e-2, weight_decay=0.01, step=step, param_out=pout)
+    close(master, ref_p.data, 1e-4, 1e-5)
+    close(pout, ref_p.data, 1e-2, 1e-2)
+    # skip flag: nothing may change
+    before = master.clone()
+    flag = torch.ones(1, dtype=torch.int32, device=dev)
+    O.adamw_step(master, m, v, torch.randn(n, device=dev).to(gdt), lr=1e-2, step=4, skip_flag=flag)
+    assert torch.equal(before, master)
+
+
+@pytest.mark.parametrize("dev", DEVS)
+def test_sumsq_clip_and_nonfinite(dev):
+    torch.manual_seed(6)
+    g = torch.randn(100003, device=dev).bfloat16()
+    out = torch.zeros(1, device=dev)
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    O.sumsq(g, out, nonfinite_flag=flag)
+    close(out, g.float().pow(2).sum()[None], 1e-3, 1e-1)
+    assert int(flag.item()) == 0
+    O.sumsq(g.float(), out, accumulate=True)
+    close(out, 2 * g.float().pow(2).sum()[None], 1e-3, 2e-1)
+    coef, nrm = torch.zeros(1, device=dev), torch.zeros(1, device=dev)
+    O.clip_coef(out, 1.0, 0.5, coef, nrm, flag)
+    close(coef, torch.tensor([0.5 / float(out.sqrt())]), 1e-3, 1e-6)
+    g[77] = float("nan")
+    O.sumsq(g, out, nonfinite_flag=flag)
+    assert int(flag.item()) == 1
+
+
+@pytest.mark.parametrize("dev", DEVS)
+def test_casts(dev):
+    x = torch.randn(1001, device=dev)
+    b = torch.empty(1001, device=dev, dtype=torch.bfloat16)
+    O.cast_to_bf16(x, b)
+    assert torch.equal(b, x.bfloat16())
+    f = torch.empty(1001, device=dev)
+    O.cast_to_f32(b, f)
+    assert torch.equal(f, b.float())
