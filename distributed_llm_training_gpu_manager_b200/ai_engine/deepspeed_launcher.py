@@ -445,6 +445,9 @@ class DeepSpeedLauncher:
             return result
         env = dict(os.environ, MASTER_ADDR=config.master_addr, MASTER_PORT=str(config.master_port),
                    B200ZERO_JOB_ID=job_id)
+        if self.engine == "native":  # make `python -m <pkg>.engine.launch` importable from any cwd
+            pkg_parent = str(Path(__file__).resolve().parents[2])
+            env["PYTHONPATH"] = pkg_parent + (os.pathsep + env["PYTHONPATH"] if env.get("PYTHONPATH") else "")
         try:
             rec = self.registry.spawn(job_id, argv, env, config_path)
             result.status = "launched"

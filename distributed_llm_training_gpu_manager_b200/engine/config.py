@@ -1,0 +1,151 @@
+"""Engine-side view of the DeepSpeed-schema JSON that ``DeepSpeedLauncher.generate_config``
+emits (every key of ref ``ai_engine/deepspeed_launcher.py:124-238`` is consumed here; the
+reference only writes them to a file for the DeepSpeed CLI). Unknown keys are kept in
+``raw`` so a config survives a save/load round trip unchanged."""
+from __future__ import annotations
+
+import json
+from dataclasses import dataclass, field
+from typing import Any, Dict, Optional, Union
+
+import torch
+
+
+@dataclass
+class EngineConfig:
+    micro_batch: int = 1
+    grad_accum: int = 1
+    grad_clip: float = 0.0
+    steps_per_print: int = 100
+    wall_clock_breakdown: bool = False
+    # zero
+    stage: int = 0
+    reduce_bucket_size: int = 500_000_000
+    allgather_bucket_size: int = 500_000_000
+    overlap_comm: bool = True
+    reduce_scatter: bool = True
+    contiguous_gradients: bool = True
+    max_live_parameters: int = 1_000_000_000
+    max_reuse_distance: int = 1_000_000_000
+    prefetch_bucket_size: int = 500_000_000
+    persistence_threshold: int = 100_000
+    gather_16bit_on_save: bool = True
+    sub_group_size: int = 1_000_000_000
+    offload_optimizer: str = "none"
+    offload_param: str = "none"
+    pin_memory: bool = True
+    # precision
+    precision: str = "fp32"  # fp32 | fp16 | bf16
+    loss_scale: float = 0.0
+    loss_scale_window: int = 1000
+    initial_scale_power: int = 16
+    hysteresis: int = 2
+    min_loss_scale: float = 1.0
+    comm_dtype: Optional[str] = None
+    prescale_gradients: bool = False
+    predivide_factor: float = 1.0
+    grad_accum_dtype: Optional[str] = None  # None -> compute dtype when grad_accum == 1 else fp32
+    # optimizer / schedule
+    lr: float = 1e-3
+    betas: tuple = (0.9, 0.999)
+    eps: float = 1e-8
+    weight_decay: float = 0.01
+    sched_type: Optional[str] = None
+    sched_params: Dict[str, Any] = field(default_factory=dict)
+    # activation checkpointing
+    act_ckpt: bool = False
+    cpu_checkpointing: bool = False
+    # elasticity
+    elastic: Dict[str, Any] = field(default_factory=dict)
+    raw: Dict[str, Any] = field(default_factory=dict)
+
+    @property
+    def compute_dtype(self) -> torch.dtype:
+        return {"fp32": torch.float32, "fp16": torch.float16, "bf16": torch.bfloat16}[self.precision]
+
+    @property
+    def reduce_dtype(self) -> torch.dtype:
+        # The reference emits communication_data_type "fp16" unconditionally, even under bf16
+        # (SURVEY.md §2.3); reducing bf16 gradients in fp16 would overflow, so fp16 is honoured
+        # only for fp16 compute and otherwise mapped to the compute dtype.
+        name = (self.comm_dtype or "").lower()
+        if name in ("fp32", "float32"):
+            return torch.float32
+        if name in ("bf16", "bfloat16") and self.precision != "fp16":
+            return torch.bfloat16 if self.precision == "bf16" else torch.float32
+        if name in ("fp16", "float16") and self.precision == "fp16":
+            return torch.float16
+        return self.compute_dtype
+
+    @property
+    def accum_dtype(self) -> torch.dtype:
+        if self.grad_accum_dtype:
+            return {"fp32": torch.float32, "bf16": torch.bfloat16, "fp16": torch.float16}[self.grad_accum_dtype]
+        if self.precision == "fp32" or self.grad_accum > 1:
+            return torch.float32
+        return self.compute_dtype
+
+    def train_batch_size(self, world_size: int) -> int:
+        return self.micro_batch * self.grad_accum * world_size
+
+
+def load_config(src: Union[str, Dict[str, Any], EngineConfig]) -> EngineConfig:
+    if isinstance(src, EngineConfig):
+        return src
+    if isinstance(src, str):
+        with open(src) as f:
+            src = json.load(f)
+    d = dict(src)
+    z = d.get("zero_optimization", {}) or {}
+    c = EngineConfig(raw=d)
+    c.micro_batch = int(d.get("train_micro_batch_size_per_gpu", 1))
+    c.grad_accum = int(d.get("gradient_accumulation_steps", 1))
+    c.grad_clip = float(d.get("gradient_clipping", 0.0))
+    c.steps_per_print = int(d.get("steps_per_print", 100))
+    c.wall_clock_breakdown = bool(d.get("wall_clock_breakdown", False))
+    c.stage = int(z.get("stage", 0))
+    c.reduce_bucket_size = int(z.get("reduce_bucket_size", c.reduce_bucket_size))
+    c.allgather_bucket_size = int(z.get("allgather_bucket_size", c.allgather_bucket_size))
+    c.overlap_comm = bool(z.get("overlap_comm", True))
+    c.reduce_scatter = bool(z.get("reduce_scatter", True))
+    c.contiguous_gradients = bool(z.get("contiguous_gradients", True))
+    c.max_live_parameters = int(z.get("stage3_max_live_parameters", c.max_live_parameters))
+    c.max_reuse_distance = int(z.get("stage3_max_reuse_distance", c.max_reuse_distance))
+    c.prefetch_bucket_size = int(z.get("stage3_prefetch_bucket_size", c.prefetch_bucket_size))
+    # below stage 3 nothing needs to stay resident, so only tiny tensors are left unpartitioned
+    c.persistence_threshold = int(z.get("stage3_param_persistence_threshold",
+                                        c.persistence_threshold if c.stage >= 3 else 4096))
+    c.gather_16bit_on_save = bool(z.get("stage3_gather_16bit_weights_on_model_save", True))
+    c.sub_group_size = int(z.get("sub_group_size", c.sub_group_size))
+    oo, op = z.get("offload_optimizer") or {}, z.get("offload_param") or {}
+    # offload blocks are emitted for any stage by the launcher; they only apply where meaningful
+    c.offload_optimizer = oo.get("device", "none") if c.stage >= 1 else "none"
+    c.offload_param = op.get("device", "none") if c.stage >= 3 else "none"
+    c.pin_memory = bool(oo.get("pin_memory", True))
+    if (d.get("bf16") or {}).get("enabled"):
+        c.precision = "bf16"
+    elif (d.get("fp16") or {}).get("enabled"):
+        c.precision = "fp16"
+        f16 = d["fp16"]
+        c.loss_scale = float(f16.get("loss_scale", 0))
+        c.loss_scale_window = int(f16.get("loss_scale_window", 1000))
+        c.initial_scale_power = int(f16.get("initial_scale_power", 16))
+        c.hysteresis = int(f16.get("hysteresis", 2))
+        c.min_loss_scale = float(f16.get("min_loss_scale", 1))
+    c.comm_dtype = d.get("communication_data_type")
+    c.prescale_gradients = bool(d.get("prescale_gradients", False))
+    c.predivide_factor = float(d.get("gradient_predivide_factor", 1.0))
+    c.grad_accum_dtype = (d.get("data_types") or {}).get("grad_accum_dtype")
+    opt = (d.get("optimizer") or {}).get("params", {})
+    c.lr = float(opt.get("lr", c.lr))
+    c.betas = tuple(opt.get("betas", c.betas))
+    c.eps = float(opt.get("eps", c.eps))
+    c.weight_decay = float(opt.get("weight_decay", c.weight_decay))
+    sch = d.get("scheduler") or {}
+    c.sched_type = sch.get("type")
+    c.sched_params = dict(sch.get("params", {}))
+    ac = d.get("activation_checkpointing")
+    c.act_ckpt = ac is not None
+    c.cpu_checkpointing = bool((ac or {}).get("cpu_checkpointing", False))
+    c.elastic = dict(d.get("elasticity") or {})
+    return c

@@ -1,0 +1,563 @@
+"""ZeRO-0/1/2/3 training engine for arbitrary ``torch.nn.Module`` models.
+
+This is the engine the reference only *configures*: its launcher emits a DeepSpeed JSON and
+shells out (ref ``ai_engine/deepspeed_launcher.py:302-367``); nothing in that tree partitions,
+reduces or steps anything. The user-facing protocol mirrors DeepSpeed's so a
+training script ports by changing one import::
+
+    engine = initialize(model=model, config="ds_config.json")
+    loss = engine(ids, labels); engine.backward(loss); engine.step()
+    engine.save_checkpoint(dir); engine.load_checkpoint(dir)
+
+Design (see ``partition.py`` for the layout):
+
+* One process per GPU, ``torch.distributed`` (NCCL on GPUs, gloo on CPU — the CPU tier runs the
+  same code and is the oracle for the fused kernels).
+* Parameters live in flat buffers; ``param.data`` and ``param.grad`` are *views* into them, bound
+  once at construction. Stage ≤ 2 keeps every unit gathered; stage 3 keeps only the root unit and
+  two block-sized buffers (even/odd blocks) alive, re-filled by all-gather just before a block
+  runs (forward, recompute and backward) and prefetched one block ahead on a side stream.
+* Gradients: autograd accumulates straight into the unit's gradient buffer; when the last
+  parameter of a unit has its gradient (post-accumulate hooks), the unit is reduce-scattered
+  into the rank's gradient shard on the communication stream (stage ≥ 2: every micro-step;
+  stage ≤ 1: at the accumulation boundary).
+* ``step()``: ‖g‖² + isfinite on the shard → one 3-float all-reduce (Σ‖g‖², non-finite flag,
+  loss) → clip coefficient on device → fused AdamW predicated on the flag → bf16 write-back →
+  (stage ≤ 2) all-gather of updated rows. The only host sync is the read of those 3 floats,
+  which feeds :class:`LossSpikeMonitor` for the halt / rollback decision.
+* ``comm="fused"`` swaps the NCCL reduce-scatter / all-gather for the in-kernel peer-memory
+  versions (``parallel/fused.py``: K1/K3).
+"""
+from __future__ import annotations
+
+import math
+import os
+import time
+from contextlib import contextmanager, nullcontext
+from typing import Any, Callable, Dict, Iterable, List, Optional, Tuple, Union
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..ops import optim as O
+from .config import EngineConfig, load_config
+from .partition import Layout, ParamSpec, UnitLayout, build_layout
+from .schedules import DynamicLossScaler, LRSchedule
+
+_BLOCK_LIST_NAMES = ("blocks", "layers", "h", "transformer_blocks")
+
+
+def _dist_ready() -> bool:
+    return dist.is_available() and dist.is_initialized()
+
+
+def discover_units(module: nn.Module) -> Tuple[List[str], List[nn.Module], Dict[int, int]]:
+    """Unit 0 = root (everything outside the block list); units 1.. = transformer blocks."""
+    blocks: List[nn.Module] = []
+    for name in _BLOCK_LIST_NAMES:
+        child = getattr(module, name, None)
+        if isinstance(child, nn.ModuleList) and len(child) > 0:
+            blocks = list(child)
+            break
+    unit_of: Dict[int, int] = {}
+    for bi, blk in enumerate(blocks):
+        for p in blk.parameters():
+            unit_of.setdefault(id(p), bi + 1)
+    names = ["root"] + [f"block{i}" for i in range(len(blocks))]
+    return names, blocks, unit_of
+
+
+class PhaseTimers:
+    """CUDA-event (or perf_counter) timers per phase; ``wall_clock_breakdown`` keeps its meaning
+    (ref ``deepspeed_launcher.py:79,129``)."""
+
+    def __init__(self, enabled: bool, cuda: bool):
+        self.enabled, self.cuda = enabled, cuda
+        self.totals: Dict[str, float] = {}
+        self._open: List[Tuple[str, Any, Any]] = []
+
+    @contextmanager
+    def phase(self, name: str):
+        if not self.enabled:
+            yield
+            return
+        if self.cuda:
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            yield
+            e.record()
+            self._open.append((name, s, e))
+        else:
+            t0 = time.perf_counter()
+            yield
+            self.totals[name] = self.totals.get(name, 0.0) + (time.perf_counter() - t0) * 1e3
+
+    def collect(self) -> Dict[str, float]:
+        if self.cuda and self._open:
+            torch.cuda.synchronize()
+            for name, s, e in self._open:
+                self.totals[name] = self.totals.get(name, 0.0) + s.elapsed_time(e)
+            self._open.clear()
+        out, self.totals = self.totals, {}
+        return out
+
+
+class ZeroEngine:
+    def __init__(self, module: nn.Module, config: Union[str, Dict[str, Any], EngineConfig], *,
+                 device: Optional[torch.device] = None, comm: str = "auto", broadcast_init: bool = True):
+        self.cfg = load_config(config)
+        self.module = module
+        self.rank = dist.get_rank() if _dist_ready() else 0
+        self.world_size = dist.get_world_size() if _dist_ready() else 1
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+        self.device = torch.device(device)
+        self.on_cuda = self.device.type == "cuda"
+        cfg = self.cfg
+        self.stage = cfg.stage
+        self.compute_dtype = cfg.compute_dtype
+        self.global_steps = 0
+        self.global_samples = 0
+        self.micro_steps = 0
+        self.skipped_steps = 0
+        self.scaler = DynamicLossScaler(cfg.precision == "fp16", cfg.loss_scale, cfg.initial_scale_power,
+                                        cfg.loss_scale_window, cfg.hysteresis, cfg.min_loss_scale)
+        self.schedule = LRSchedule(cfg.sched_type, cfg.sched_params, cfg.lr)
+        self.timers = PhaseTimers(cfg.wall_clock_breakdown, self.on_cuda)
+        self.comm_stream = torch.cuda.Stream(device=self.device) if self.on_cuda else None
+        self.comm_mode = comm
+        self._loss_accum = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self.last_metrics: Dict[str, float] = {}
+        self.fault_hooks: Dict[str, Callable] = {}
+        self.fused = None
+        self._in_backward = False
+        self._reduce_now = True
+        self._prefetch_evt: Dict[int, Any] = {}
+
+        # ---- parameters, units, layout ----
+        module.to(self.device)
+        unit_names, self.blocks, unit_of = discover_units(module)
+        seen, plist = set(), []
+        for name, p in module.named_parameters():
+            if id(p) in seen:
+                continue
+            seen.add(id(p))
+            plist.append((name, p, unit_of.get(id(p), 0)))
+        self.named_params: List[Tuple[str, nn.Parameter]] = [(n, p) for n, p, _ in plist]
+        self.layout: Layout = build_layout([(n, tuple(p.shape), u) for n, p, u in plist], unit_names, self.world_size,
+                                           partition=self.stage >= 1, persistence_threshold=cfg.persistence_threshold)
+        self._param_of: Dict[str, nn.Parameter] = {n: p for n, p, _ in plist}
+        if getattr(module, "activation_checkpointing", None) is not None:
+            module.activation_checkpointing = cfg.act_ckpt
+        if broadcast_init and self.world_size > 1:
+            for _, p in self.named_params:  # X7: identical start on every rank
+                dist.broadcast(p.data, src=0)
+        self._build_buffers()
+        self._install_hooks()
+        if self.comm_mode == "auto":
+            self.comm_mode = "nccl" if self.on_cuda else "gloo"
+        if self.comm_mode == "fused":
+            from ..parallel.fused import FusedComm
+            self.fused = FusedComm(self)
+
+    # ------------------------------------------------------------------ buffers
+    def _slice_rows(self, spec: ParamSpec, full: torch.Tensor) -> torch.Tensor:
+        if not spec.partitioned:
+            return full.reshape(-1)
+        rows = spec.shape[0] // self.world_size
+        return full[self.rank * rows:(self.rank + 1) * rows].reshape(-1)
+
+    def _build_buffers(self) -> None:
+        L, cfg, dev, cd = self.layout, self.cfg, self.device, self.compute_dtype
+        state_dev = torch.device("cpu") if cfg.offload_optimizer in ("cpu", "nvme") else dev
+        pin = state_dev.type == "cpu" and self.on_cuda and cfg.pin_memory
+        mk = lambda: torch.zeros(L.shard_numel, dtype=torch.float32, device=state_dev, pin_memory=pin)  # noqa: E731
+        self.master, self.exp_avg, self.exp_avg_sq = mk(), mk(), mk()
+        self.state_device = state_dev
+        self.shard_grads = torch.zeros(L.shard_numel, dtype=cfg.accum_dtype, device=dev)
+        self.shard_params = torch.zeros(L.shard_numel, dtype=cd, device=dev)
+        # master <- current (fp32) parameter values, own rows only
+        for u in L.units:
+            for spec in u.params:
+                p = self._param_of[spec.name]
+                src = self._slice_rows(spec, p.data.detach().float())
+                self.master[spec.shard_offset:spec.shard_offset + spec.shard_numel].copy_(src)
+        self.shard_params.copy_(self.master.to(dev, non_blocking=False).to(cd))
+        # parameter / gradient buffers
+        nblk = len(L.units) - 1
+        if self.stage >= 3 and nblk >= 2:
+            blk_numel = max(u.full_numel for u in L.units[1:])
+            self._pbuf_root = torch.zeros(L.units[0].full_numel, dtype=cd, device=dev)
+            self._pbuf_blk = [torch.zeros(blk_numel, dtype=cd, device=dev) for _ in range(2)]
+            self._unit_pbuf = [self._pbuf_root] + [self._pbuf_blk[(i - 1) % 2] for i in range(1, len(L.units))]
+            self._resident = [False] * len(L.units)      # which unit's weights currently sit in its buffer
+            self._slot_owner: List[Optional[int]] = [None, None]
+        else:
+            total = sum(u.full_numel for u in L.units)
+            self._pbuf_all = torch.zeros(total, dtype=cd, device=dev)
+            off, self._unit_pbuf = 0, []
+            for u in L.units:
+                self._unit_pbuf.append(self._pbuf_all[off:off + u.full_numel])
+                off += u.full_numel
+            self._resident = [True] * len(L.units)
+            self._slot_owner = [None, None]
+        self.pooled_params = self.stage >= 3 and nblk >= 2
+        self.pooled_grads = self.stage >= 2 and nblk >= 2
+        if self.pooled_grads:
+            blk_numel = max(u.full_numel for u in L.units[1:])
+            self._gbuf_root = torch.zeros(L.units[0].full_numel, dtype=cd, device=dev)
+            self._gbuf_blk = [torch.zeros(blk_numel, dtype=cd, device=dev) for _ in range(2)]
+            self._unit_gbuf = [self._gbuf_root] + [self._gbuf_blk[(i - 1) % 2] for i in range(1, len(L.units))]
+        else:
+            total = sum(u.full_numel for u in L.units)
+            self._gbuf_all = torch.zeros(total, dtype=cd, device=dev)
+            off, self._unit_gbuf = 0, []
+            for u in L.units:
+                self._unit_gbuf.append(self._gbuf_all[off:off + u.full_numel])
+                off += u.full_numel
+        self._gslot_free_evt: List[Optional[Any]] = [None, None]  # grad pool slot reusable after this event
+        # bind param.data / param.grad views (once)
+        for u in L.units:
+            pb, gb = self._unit_pbuf[u.index], self._unit_gbuf[u.index]
+            for spec in u.params:
+                p = self._param_of[spec.name]
+                view = pb[spec.full_offset:spec.full_offset + spec.numel].view(spec.shape)
+                if self._resident[u.index]:
+                    view.copy_(p.data.to(cd))
+                p.data = view
+                p.grad = gb[spec.full_offset:spec.full_offset + spec.numel].view(spec.shape)
+        # small scalars used by step()
+        self._stats = torch.zeros(4, dtype=torch.float32, device=dev)      # [sumsq_part, nonfinite, loss, sumsq_repl]
+        self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._coef = torch.ones(1, dtype=torch.float32, device=dev)
+        self._norm = torch.zeros(1, dtype=torch.float32, device=dev)
+        self._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
+        if self.on_cuda:
+            self._stats_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+        if self.stage >= 3 and self.pooled_params:
+            self._gather_unit(0)
+
+    # ------------------------------------------------------------------ hooks
+    def _install_hooks(self) -> None:
+        L = self.layout
+        self._pending = [0] * len(L.units)
+        self._need = [sum(1 for s in u.params if self._param_of[s.name].requires_grad) for u in L.units]
+        self._reduced = [False] * len(L.units)
+        for u in L.units:
+            for spec in u.params:
+                p = self._param_of[spec.name]
+                if p.requires_grad:
+                    p.register_post_accumulate_grad_hook(self._make_grad_hook(u.index))
+        for bi, blk in enumerate(self.blocks):
+            ui = bi + 1
+            blk.register_forward_pre_hook(self._make_pre_fwd(ui))
+            blk.register_full_backward_pre_hook(self._make_pre_bwd(ui))
+
+    def _make_grad_hook(self, ui: int):
+        def hook(_p):
+            self._pending[ui] -= 1
+            if self._pending[ui] == 0 and self._reduce_now:
+                self._reduce_unit(ui)
+        return hook
+
+    def _make_pre_fwd(self, ui: int):
+        def hook(_m, _inp):
+            if self.pooled_params:
+                self._ensure_resident(ui)
+                nxt = ui + 1 if not self._in_backward else ui - 1
+                if 1 <= nxt < len(self.layout.units):
+                    self._prefetch(nxt)
+        return hook
+
+    def _make_pre_bwd(self, ui: int):
+        def hook(_m, _gout):
+            if self.pooled_params:
+                self._ensure_resident(ui)
+                if ui - 1 >= 1:
+                    self._prefetch(ui - 1)
+            if self.pooled_grads:
+                evt = self._gslot_free_evt[(ui - 1) % 2]
+                if evt is not None and self.on_cuda:
+                    torch.cuda.current_stream().wait_event(evt)
+        return hook
+
+    # ------------------------------------------------------------------ stage-3 parameter residency
+    def _gather_unit(self, ui: int, stream=None) -> None:
+        """All-gather unit ``ui``'s rows into its buffer (X2). Replicated tensors are local copies."""
+        u = self.layout.units[ui]
+        pb = self._unit_pbuf[ui]
+        ctx = torch.cuda.stream(stream) if (stream is not None and self.on_cuda) else nullcontext()
+        with ctx:
+            if self.fused is not None and self.fused.gather_unit(ui):
+                pass
+            else:
+                for spec in u.params:
+                    dst = pb[spec.full_offset:spec.full_offset + spec.numel]
+                    src = self.shard_params[spec.shard_offset:spec.shard_offset + spec.shard_numel]
+                    if spec.partitioned:
+                        _all_gather(dst, src)
+                    else:
+                        dst.copy_(src)
+        self._resident[ui] = True
+        if ui >= 1 and self.pooled_params:
+            slot = (ui - 1) % 2
+            prev = self._slot_owner[slot]
+            if prev is not None and prev != ui:
+                self._resident[prev] = False
+            self._slot_owner[slot] = ui
+
+    def _ensure_resident(self, ui: int) -> None:
+        if self._resident[ui] and (ui == 0 or self._slot_owner[(ui - 1) % 2] == ui):
+            evt = self._prefetch_evt.pop(ui, None)
+            if evt is not None:
+                torch.cuda.current_stream().wait_event(evt)
+            return
+        self._gather_unit(ui)
+
+    def _prefetch(self, ui: int) -> None:
+        """Issue the gather of unit ``ui`` on the comm stream (``stage3_prefetch_bucket_size`` > 0)."""
+        if self._resident[ui] and self._slot_owner[(ui - 1) % 2] == ui:
+            return
+        if not self.on_cuda or not self.cfg.overlap_comm or self.cfg.prefetch_bucket_size <= 0:
+            return  # gathered synchronously on demand
+        # the slot's previous owner (ui±2) finished executing before the block that triggered us started
+        self.comm_stream.wait_stream(torch.cuda.current_stream())
+        self._gather_unit(ui, stream=self.comm_stream)
+        evt = torch.cuda.Event()
+        evt.record(self.comm_stream)
+        self._prefetch_evt[ui] = evt
+
+    # ------------------------------------------------------------------ gradient reduction
+    def _reduce_unit(self, ui: int) -> None:
+        """Reduce-scatter (X1) / all-reduce (X4) unit ``ui``'s gradients into the rank's shard."""
+        if self._reduced[ui]:
+            return
+        self._reduced[ui] = True
+        u = self.layout.units[ui]
+        gb = self._unit_gbuf[ui]
+        use_side = self.on_cuda and self.cfg.overlap_comm
+        if use_side:
+            self.comm_stream.wait_stream(torch.cuda.current_stream())
+        ctx = torch.cuda.stream(self.comm_stream) if use_side else nullcontext()
+        scale = 1.0 / self.world_size  # mean over data-parallel ranks
+        with ctx, self.timers.phase("reduce"):
+            if self.fused is not None and self.fused.reduce_unit(ui, scale):
+                pass
+            else:
+                rdt = self.cfg.reduce_dtype
+                for spec in u.params:
+                    g = gb[spec.full_offset:spec.full_offset + spec.numel]
+                    dst = self.shard_grads[spec.shard_offset:spec.shard_offset + spec.shard_numel]
+                    if self.world_size == 1:
+                        dst.add_(g.to(dst.dtype))
+                        continue
+                    gr = g if g.dtype == rdt else g.to(rdt)
+                    if spec.partitioned:
+                        dst.add_(_reduce_scatter(gr, self.rank, self.world_size).to(dst.dtype), alpha=scale)
+                    else:
+                        dist.all_reduce(gr)
+                        dst.add_(gr.to(dst.dtype), alpha=scale)
+            gb.zero_()
+            if use_side and self.pooled_grads and ui >= 1:
+                evt = torch.cuda.Event()
+                evt.record(self.comm_stream)
+                self._gslot_free_evt[(ui - 1) % 2] = evt
+
+    # ------------------------------------------------------------------ public protocol
+    def __call__(self, *args, **kwargs):
+        return self.forward(*args, **kwargs)
+
+    def train(self, mode: bool = True):
+        self.module.train(mode)
+        return self
+
+    def eval(self):
+        return self.train(False)
+
+    def is_gradient_accumulation_boundary(self) -> bool:
+        return (self.micro_steps + 1) % self.cfg.grad_accum == 0
+
+    def forward(self, *args, **kwargs):
+        self._in_backward = False
+        if self.pooled_params:
+            self._ensure_resident(0)
+        with self.timers.phase("forward"):
+            return self.module(*args, **kwargs)
+
+    def backward(self, loss: torch.Tensor) -> None:
+        cfg = self.cfg
+        self._in_backward = True
+        boundary = self.is_gradient_accumulation_boundary()
+        self._reduce_now = self.stage >= 2 or boundary
+        self._pending = list(self._need)
+        self._reduced = [False] * len(self.layout.units)
+        hook = self.fault_hooks.get("pre_backward")
+        if hook is not None:
+            loss = hook(self, loss)
+        self._loss_accum += loss.detach().float() / cfg.grad_accum
+        with self.timers.phase("backward"):
+            (loss * (self.scaler.scale / cfg.grad_accum)).backward()
+        if self._reduce_now:
+            for ui in range(len(self.layout.units) - 1, -1, -1):  # units whose hooks never all fired
+                if not self._reduced[ui]:
+                    self._reduce_unit(ui)
+        if self.on_cuda and cfg.overlap_comm:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        hook = self.fault_hooks.get("post_backward")
+        if hook is not None:
+            hook(self)
+        self._in_backward = False
+
+    def step(self) -> Optional[Dict[str, float]]:
+        """Call after every ``backward``; does the optimizer step at accumulation boundaries.
+        Returns the step's metrics dict at a boundary, else None."""
+        self.micro_steps += 1
+        self.global_samples += self.cfg.micro_batch * self.world_size
+        if self.micro_steps % self.cfg.grad_accum != 0:
+            return None
+        return self._optimizer_step()
+
+    # ------------------------------------------------------------------ optimizer step
+    def _optimizer_step(self) -> Dict[str, float]:
+        cfg, L = self.cfg, self.layout
+        with self.timers.phase("step"):
+            self._flag.zero_()
+            st = self._stats
+            st.zero_()
+            O.sumsq(self.shard_grads[:L.part_numel], st[0:1], nonfinite_flag=self._flag) if L.part_numel else None
+            if L.shard_numel > L.part_numel:
+                O.sumsq(self.shard_grads[L.part_numel:], st[3:4], nonfinite_flag=self._flag)
+            st[1] = self._flag.float()[0]
+            st[2] = self._loss_accum[0] / self.world_size
+            if self.world_size > 1:
+                repl = st[3].clone()
+                st[3] = 0
+                dist.all_reduce(st)           # Σ‖g‖² (X6), overflow flag (X5), mean loss (X8) in one message
+                st[3] = repl
+            self._sumsq[0] = st[0] + st[3]
+            self._flag[0] = (st[1] > 0).int()
+            inv_scale = 1.0 / self.scaler.scale
+            O.clip_coef(self._sumsq, cfg.grad_clip * self.scaler.scale if cfg.grad_clip > 0 else 0.0, inv_scale,
+                        self._coef, self._norm, self._flag)
+            lr = self.schedule.lr_at(self.global_steps)
+            step_no = self.global_steps - self.skipped_steps + 1
+            if self.state_device.type == "cpu" and self.on_cuda:
+                self._offloaded_adam(lr, step_no)
+            else:
+                O.adamw_step(self.master, self.exp_avg, self.exp_avg_sq, self.shard_grads, lr=lr, beta1=cfg.betas[0],
+                             beta2=cfg.betas[1], eps=cfg.eps, weight_decay=cfg.weight_decay, step=step_no,
+                             grad_scale_dev=self._coef, skip_flag=self._flag,
+                             param_out=self.shard_params if self.compute_dtype == torch.bfloat16 and self.on_cuda else None)
+                if not (self.compute_dtype == torch.bfloat16 and self.on_cuda):
+                    self.shard_params.copy_(self.master.to(self.compute_dtype))
+            self.shard_grads.zero_()
+            # host read: the one sync of the step (feeds the loss monitor)
+            if self.on_cuda:
+                self._stats_host.copy_(torch.stack([self._sumsq[0], self._flag[0].float(), st[2], self._norm[0] * inv_scale]),
+                                       non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                vals = self._stats_host.tolist()
+            else:
+                vals = [float(self._sumsq[0]), float(self._flag[0]), float(st[2]), float(self._norm[0]) * inv_scale]
+            overflow = vals[1] > 0
+            self.scaler.update(overflow)
+            if overflow:
+                self.skipped_steps += 1
+            # updated rows -> everyone (X3); stage 3 re-gathers lazily instead
+            with self.timers.phase("allgather"):
+                if self.stage >= 3 and self.pooled_params:
+                    self._resident = [False] * len(L.units)
+                    self._slot_owner = [None, None]
+                    self._gather_unit(0)
+                else:
+                    for ui in range(len(L.units)):
+                        self._gather_unit(ui)
+            self._loss_accum.zero_()
+        self.global_steps += 1
+        self.schedule.last_step = self.global_steps
+        m = {"step": self.global_steps, "loss": vals[2], "grad_norm": vals[3], "grad_norm_sq": vals[3] ** 2,
+             "nonfinite": overflow, "lr": lr, "loss_scale": self.scaler.scale, "skipped": overflow}
+        if cfg.wall_clock_breakdown:
+            m["timers_ms"] = self.timers.collect()
+        self.last_metrics = m
+        return m
+
+    def _offloaded_adam(self, lr: float, step_no: int) -> None:
+        from .offload import host_adam_step
+        host_adam_step(self, lr, step_no)
+
+    # ------------------------------------------------------------------ introspection / state
+    def get_lr(self) -> List[float]:
+        return [self.schedule.lr_at(self.global_steps)]
+
+    def memory_report(self) -> Dict[str, float]:
+        gib = float(1 << 30)
+        L = self.layout
+        pbufs = {b.data_ptr(): b for b in self._unit_pbuf}
+        gbufs = {b.data_ptr(): b for b in self._unit_gbuf}
+        return {"params_total": L.total_params, "shard_numel": L.shard_numel,
+                "optimizer_state_gib": 3 * L.shard_numel * 4 / gib,
+                "grad_shard_gib": L.shard_numel * self.shard_grads.element_size() / gib,
+                "param_buffers_gib": sum(b.numel() * b.element_size() for b in pbufs.values()) / gib,
+                "grad_buffers_gib": sum(b.numel() * b.element_size() for b in gbufs.values()) / gib}
+
+    def full_param(self, name: str) -> torch.Tensor:
+        """Gathered fp32 master copy of one parameter (collective when partitioned)."""
+        spec = self.layout.by_name[name]
+        local = self.master[spec.shard_offset:spec.shard_offset + spec.shard_numel].to(self.device)
+        if not spec.partitioned:
+            return local.view(spec.shape).clone()
+        out = torch.empty(spec.numel, dtype=torch.float32, device=self.device)
+        _all_gather(out, local.contiguous())
+        return out.view(spec.shape)
+
+    def module_state_dict(self) -> Dict[str, torch.Tensor]:
+        """16-bit (compute dtype) weights by name, gathered (``stage3_gather_16bit_weights_on_model_save``)."""
+        sd = {}
+        for u in self.layout.units:
+            if not self._resident[u.index]:
+                self._gather_unit(u.index)
+            for spec in u.params:
+                sd[spec.name] = self._param_of[spec.name].data.detach().clone().cpu()
+            if self.pooled_params and u.index >= 1:
+                pass
+        return sd
+
+    def save_checkpoint(self, save_dir: str, tag: Optional[str] = None, client_state: Optional[Dict] = None,
+                        async_write: bool = False):
+        from .checkpoint import save_checkpoint
+        return save_checkpoint(self, save_dir, tag, client_state or {}, async_write=async_write)
+
+    def load_checkpoint(self, load_dir: str, tag: Optional[str] = None):
+        from .checkpoint import load_checkpoint
+        return load_checkpoint(self, load_dir, tag)
+
+
+# ---------------------------------------------------------------------- collectives with gloo fallbacks
+def _all_gather(dst_flat: torch.Tensor, src_flat: torch.Tensor) -> None:
+    if not _dist_ready() or dist.get_world_size() == 1:
+        dst_flat.copy_(src_flat)
+        return
+    try:
+        dist.all_gather_into_tensor(dst_flat, src_flat.contiguous())
+    except (RuntimeError, NotImplementedError):
+        ws = dist.get_world_size()
+        parts = list(dst_flat.view(ws, -1).unbind(0))
+        dist.all_gather(parts, src_flat.contiguous())
+
+
+def _reduce_scatter(full_flat: torch.Tensor, rank: int, ws: int) -> torch.Tensor:
+    n = full_flat.numel() // ws
+    if full_flat.is_cuda:
+        out = torch.empty(n, dtype=full_flat.dtype, device=full_flat.device)
+        dist.reduce_scatter_tensor(out, full_flat.contiguous())
+        return out
+    tmp = full_flat.clone()  # gloo has no reduce-scatter: all-reduce then slice
+    dist.all_reduce(tmp)
+    return tmp[rank * n:(rank + 1) * n]
+
+
+def initialize(model: nn.Module, config: Union[str, Dict[str, Any], EngineConfig], **kw) -> ZeroEngine:
+    """DeepSpeed-style constructor: ``engine = initialize(model=..., config=...)``."""
+    return ZeroEngine(model, config, **kw)
