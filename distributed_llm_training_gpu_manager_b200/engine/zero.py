@@ -103,6 +103,21 @@ class PhaseTimers:
         return out
 
 
+class ParamSource:
+    """Parameter provider for engines that own their compute path (no ``nn.Module``): names,
+    shapes and units, plus a deterministic row-range initialiser so a rank can fill its shard of
+    a 70B model without ever materialising the whole tensor."""
+
+    unit_names: List[str] = []
+
+    def specs(self) -> List[Tuple[str, Tuple[int, ...], int]]:
+        raise NotImplementedError
+
+    def init_rows(self, name: str, shape: Tuple[int, ...], r0: int, r1: int) -> torch.Tensor:
+        """fp32 tensor for rows [r0, r1) of parameter ``name`` (any device)."""
+        raise NotImplementedError
+
+
 class ZeroEngine:
     def __init__(self, module: nn.Module, config: Union[str, Dict[str, Any], EngineConfig], *,
                  device: Optional[torch.device] = None, comm: str = "auto", broadcast_init: bool = True):
@@ -136,25 +151,36 @@ class ZeroEngine:
         self._prefetch_evt: Dict[int, Any] = {}
 
         # ---- parameters, units, layout ----
-        module.to(self.device)
-        unit_names, self.blocks, unit_of = discover_units(module)
-        seen, plist = set(), []
-        for name, p in module.named_parameters():
-            if id(p) in seen:
-                continue
-            seen.add(id(p))
-            plist.append((name, p, unit_of.get(id(p), 0)))
-        self.named_params: List[Tuple[str, nn.Parameter]] = [(n, p) for n, p, _ in plist]
-        self.layout: Layout = build_layout([(n, tuple(p.shape), u) for n, p, u in plist], unit_names, self.world_size,
-                                           partition=self.stage >= 1, persistence_threshold=cfg.persistence_threshold)
-        self._param_of: Dict[str, nn.Parameter] = {n: p for n, p, _ in plist}
-        if getattr(module, "activation_checkpointing", None) is not None:
-            module.activation_checkpointing = cfg.act_ckpt
-        if broadcast_init and self.world_size > 1:
-            for _, p in self.named_params:  # X7: identical start on every rank
-                dist.broadcast(p.data, src=0)
+        self.source = module if isinstance(module, ParamSource) else None
+        if self.source is not None:
+            self.module = None
+            self.blocks = []
+            unit_names = list(self.source.unit_names)
+            specs = list(self.source.specs())
+            self.named_params = []
+            self._param_of = {}
+        else:
+            module.to(self.device)
+            unit_names, self.blocks, unit_of = discover_units(module)
+            seen, plist = set(), []
+            for name, p in module.named_parameters():
+                if id(p) in seen:
+                    continue
+                seen.add(id(p))
+                plist.append((name, p, unit_of.get(id(p), 0)))
+            self.named_params = [(n, p) for n, p, _ in plist]
+            specs = [(n, tuple(p.shape), u) for n, p, u in plist]
+            self._param_of = {n: p for n, p, _ in plist}
+            if getattr(module, "activation_checkpointing", None) is not None:
+                module.activation_checkpointing = cfg.act_ckpt
+            if broadcast_init and self.world_size > 1:
+                for _, p in self.named_params:  # X7: identical start on every rank
+                    dist.broadcast(p.data, src=0)
+        self.layout: Layout = build_layout(specs, unit_names, self.world_size, partition=self.stage >= 1,
+                                           persistence_threshold=cfg.persistence_threshold)
         self._build_buffers()
-        self._install_hooks()
+        if self.source is None:
+            self._install_hooks()
         if self.comm_mode == "auto":
             self.comm_mode = "nccl" if self.on_cuda else "gloo"
         if self.comm_mode == "fused":
@@ -177,12 +203,16 @@ class ZeroEngine:
         self.state_device = state_dev
         self.shard_grads = torch.zeros(L.shard_numel, dtype=cfg.accum_dtype, device=dev)
         self.shard_params = torch.zeros(L.shard_numel, dtype=cd, device=dev)
-        # master <- current (fp32) parameter values, own rows only
+        # master <- initial fp32 values, own rows only
         for u in L.units:
             for spec in u.params:
-                p = self._param_of[spec.name]
-                src = self._slice_rows(spec, p.data.detach().float())
-                self.master[spec.shard_offset:spec.shard_offset + spec.shard_numel].copy_(src)
+                dst = self.master[spec.shard_offset:spec.shard_offset + spec.shard_numel]
+                if self.source is not None:
+                    rows = spec.shape[0] // self.world_size if spec.partitioned else spec.shape[0]
+                    r0 = self.rank * rows if spec.partitioned else 0
+                    dst.copy_(self.source.init_rows(spec.name, spec.shape, r0, r0 + rows).reshape(-1))
+                else:
+                    dst.copy_(self._slice_rows(spec, self._param_of[spec.name].data.detach().float()))
         self.shard_params.copy_(self.master.to(dev, non_blocking=False).to(cd))
         # parameter / gradient buffers
         nblk = len(L.units) - 1
@@ -217,16 +247,20 @@ class ZeroEngine:
                 self._unit_gbuf.append(self._gbuf_all[off:off + u.full_numel])
                 off += u.full_numel
         self._gslot_free_evt: List[Optional[Any]] = [None, None]  # grad pool slot reusable after this event
-        # bind param.data / param.grad views (once)
-        for u in L.units:
-            pb, gb = self._unit_pbuf[u.index], self._unit_gbuf[u.index]
-            for spec in u.params:
-                p = self._param_of[spec.name]
-                view = pb[spec.full_offset:spec.full_offset + spec.numel].view(spec.shape)
-                if self._resident[u.index]:
-                    view.copy_(p.data.to(cd))
-                p.data = view
-                p.grad = gb[spec.full_offset:spec.full_offset + spec.numel].view(spec.shape)
+        # bind param.data / param.grad views (once); a ParamSource engine reads views on demand
+        if self.source is None:
+            for u in L.units:
+                pb, gb = self._unit_pbuf[u.index], self._unit_gbuf[u.index]
+                for spec in u.params:
+                    p = self._param_of[spec.name]
+                    view = pb[spec.full_offset:spec.full_offset + spec.numel].view(spec.shape)
+                    if self._resident[u.index]:
+                        view.copy_(p.data.to(cd))
+                    p.data = view
+                    p.grad = gb[spec.full_offset:spec.full_offset + spec.numel].view(spec.shape)
+        elif not self.pooled_params:
+            for ui in range(len(L.units)):
+                self._gather_unit(ui)
         # small scalars used by step()
         self._stats = torch.zeros(4, dtype=torch.float32, device=dev)      # [sumsq_part, nonfinite, loss, sumsq_repl]
         self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -487,6 +521,15 @@ class ZeroEngine:
         from .offload import host_adam_step
         host_adam_step(self, lr, step_no)
 
+    # ------------------------------------------------------------------ views for module-less engines
+    def param_view(self, name: str) -> torch.Tensor:
+        spec = self.layout.by_name[name]
+        return self._unit_pbuf[spec.unit][spec.full_offset:spec.full_offset + spec.numel].view(spec.shape)
+
+    def grad_view(self, name: str) -> torch.Tensor:
+        spec = self.layout.by_name[name]
+        return self._unit_gbuf[spec.unit][spec.full_offset:spec.full_offset + spec.numel].view(spec.shape)
+
     # ------------------------------------------------------------------ introspection / state
     def get_lr(self) -> List[float]:
         return [self.schedule.lr_at(self.global_steps)]
@@ -519,9 +562,7 @@ class ZeroEngine:
             if not self._resident[u.index]:
                 self._gather_unit(u.index)
             for spec in u.params:
-                sd[spec.name] = self._param_of[spec.name].data.detach().clone().cpu()
-            if self.pooled_params and u.index >= 1:
-                pass
+                sd[spec.name] = self.param_view(spec.name).detach().clone().cpu()
         return sd
 
     def save_checkpoint(self, save_dir: str, tag: Optional[str] = None, client_state: Optional[Dict] = None,

@@ -1,0 +1,246 @@
+"""Llama executed directly on the sm_100a kernels: flat ZeRO buffers, hand-written forward and
+backward (no autograd graph, no tracing compiler), per-layer activation recompute, weights
+gathered per block (ZeRO-3) and gradients reduce-scattered per block as soon as they exist.
+
+Per block (T = micro_batch·seq tokens)::
+
+    h1  = rmsnorm(x)                    K5          qkv = h1 · Wqkvᵀ        K4 (tcgen05 GEMM)
+    rope(q,k) in place                  K7          a   = flash_attn(qkv)   K6
+    x1  = x + a · Woᵀ  ; h2 = rmsnorm(x1)   K4 + fused add-norm K5
+    gu  = h2 · Wguᵀ ; act = silu(g)·u   K4 + K8     x2  = x1 + act · Wdownᵀ K4
+
+Backward recomputes the block from its saved input, then runs dgrad (B operand MN-major) and
+wgrad (both operands MN-major) GEMMs whose epilogues write straight into the block's slice of
+the gradient bucket. The LM head never materialises full logits: token chunks go
+GEMM → in-place softmax-CE (K9) → dgrad/wgrad while the chunk is still in L2.
+
+The nn.Module twin in ``models/llama.py`` is the numerical oracle (same fused weight layout).
+The reference ships no model.
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, Dict, List, Optional, Tuple, Union
+
+import torch
+import torch.distributed as dist
+
+from ..engine.config import EngineConfig, load_config
+from ..engine.zero import ParamSource, ZeroEngine
+from ..ops import attention as A
+from ..ops import elementwise as E
+from ..ops import gemm as G
+from .configs import ModelConfig
+
+
+class LlamaParams(ParamSource):
+    def __init__(self, cfg: ModelConfig, seed: int = 1234, init_device: Union[str, torch.device] = "cpu"):
+        self.cfg, self.seed, self.init_device = cfg, seed, torch.device(init_device)
+        self.unit_names = ["root"] + [f"block{i}" for i in range(cfg.n_layers)]
+
+    def specs(self):
+        c = self.cfg
+        d, hd = c.hidden, c.head_dim
+        qkv = (c.n_heads + 2 * c.n_kv_heads) * hd
+        out = [("embed.weight", (c.padded_vocab, d), 0), ("final_norm.weight", (d,), 0),
+               ("lm_head.weight", (c.padded_vocab, d), 0)]
+        for i in range(c.n_layers):
+            p = f"blocks.{i}."
+            out += [(p + "attn_norm.weight", (d,), i + 1), (p + "wqkv.weight", (qkv, d), i + 1),
+                    (p + "wo.weight", (d, d), i + 1), (p + "ffn_norm.weight", (d,), i + 1),
+                    (p + "w_gate_up.weight", (2 * c.ffn, d), i + 1), (p + "w_down.weight", (d, c.ffn), i + 1)]
+        return out
+
+    def init_rows(self, name: str, shape, r0: int, r1: int) -> torch.Tensor:
+        if name.endswith("norm.weight"):
+            return torch.ones(shape, dtype=torch.float32)[r0:r1]
+        # N(0, 0.02) per row block, seeded by (name, row-chunk) so any world size sees the same tensor
+        cols = int(shape[1])
+        out = torch.empty((r1 - r0, cols), dtype=torch.float32, device=self.init_device)
+        CH = 1024
+        base = (hash_name(name) ^ self.seed) & 0x7FFFFFFF
+        r = r0
+        while r < r1:
+            c0 = r // CH
+            lo, hi = c0 * CH, min((c0 + 1) * CH, int(shape[0]))
+            g = torch.Generator(device=self.init_device).manual_seed(base * 4099 + c0)
+            blk = torch.randn((hi - lo, cols), generator=g, device=self.init_device, dtype=torch.float32) * 0.02
+            take_hi = min(hi, r1)
+            out[r - r0: take_hi - r0] = blk[r - lo: take_hi - lo]
+            r = take_hi
+        return out
+
+
+def hash_name(name: str) -> int:
+    h = 2166136261
+    for ch in name.encode():
+        h = ((h ^ ch) * 16777619) & 0xFFFFFFFF
+    return h
+
+
+class NativeLlamaEngine(ZeroEngine):
+    """ZeRO engine whose compute path is the hand-written kernel sequence above."""
+
+    def __init__(self, model_cfg: ModelConfig, config: Union[str, Dict[str, Any], EngineConfig], *, seq_len: int,
+                 device: Optional[torch.device] = None, comm: str = "auto", seed: int = 1234,
+                 attn_backend: Optional[str] = None, head_chunk: int = 2048):
+        assert model_cfg.family == "llama"
+        ecfg = load_config(config)
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+        self.mcfg = model_cfg
+        self.seq_len = seq_len
+        self.attn_backend = attn_backend
+        self.head_chunk = head_chunk
+        src = LlamaParams(model_cfg, seed, init_device=device if torch.device(device).type == "cuda" else "cpu")
+        super().__init__(src, ecfg, device=device, comm=comm, broadcast_init=False)
+        assert self.compute_dtype == torch.bfloat16 or not self.on_cuda, "native kernels are bf16"
+        self._saved: Optional[Dict[str, Any]] = None
+        self._micro_in_window = 0
+
+    # -------------------------------------------------------------- helpers
+    def _w(self, layer: int, name: str) -> torch.Tensor:
+        return self.param_view(f"blocks.{layer}.{name}.weight")
+
+    def _gw(self, layer: int, name: str) -> torch.Tensor:
+        return self.grad_view(f"blocks.{layer}.{name}.weight")
+
+    def _block_fwd(self, l: int, x: torch.Tensor, keep: bool) -> Tuple[torch.Tensor, Optional[Dict[str, Any]]]:
+        c = self.mcfg
+        B, S = self._B, self.seq_len
+        Hq, Hk, hd, F_ = c.n_heads, c.n_kv_heads, c.head_dim, c.ffn
+        h1, rstd1, _ = E.rmsnorm_fwd(x, self._w(l, "attn_norm"), c.norm_eps)
+        qkv = G.linear_fwd(h1, self._w(l, "wqkv"))
+        E.rope_(qkv, S, Hq + Hk, hd, c.rope_theta)
+        attn, actx = A.attention_fwd(qkv, B, S, Hq, Hk, hd, backend=self.attn_backend)
+        o = G.linear_fwd(attn, self._w(l, "wo"))
+        h2, rstd2, x1 = E.rmsnorm_fwd(x, self._w(l, "ffn_norm"), c.norm_eps, delta=o)
+        gu = G.linear_fwd(h2, self._w(l, "w_gate_up"))
+        act = E.swiglu_fwd(gu)
+        dn = G.linear_fwd(act, self._w(l, "w_down"))
+        x2 = E.add(x1, dn, out=dn)
+        if not keep:
+            return x2, None
+        return x2, dict(h1=h1, rstd1=rstd1, attn=attn, actx=actx, x1=x1, rstd2=rstd2, h2=h2, gu=gu, act=act)
+
+    def _block_bwd(self, l: int, x: torch.Tensor, dx2: torch.Tensor, acc: bool) -> torch.Tensor:
+        c = self.mcfg
+        S = self.seq_len
+        Hq, Hk, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        _, sv = self._block_fwd(l, x, keep=True)                      # recompute
+        adt = dict(accumulate=acc)
+        # MLP
+        G.linear_wgrad(dx2, sv["act"], out=self._gw(l, "w_down"), **adt)
+        dact = G.linear_dgrad(dx2, self._w(l, "w_down"))
+        dgu = E.swiglu_bwd(sv["gu"], dact)
+        del dact
+        G.linear_wgrad(dgu, sv["h2"], out=self._gw(l, "w_gate_up"), **adt)
+        dh2 = G.linear_dgrad(dgu, self._w(l, "w_gate_up"))
+        del dgu
+        dx1, _ = E.rmsnorm_bwd(sv["x1"], self._w(l, "ffn_norm"), dh2, c.norm_eps, rstd=sv["rstd2"], dres=dx2,
+                               dw_out=self._gw(l, "ffn_norm"), dw_accumulate=acc, dx_out=dh2)
+        # attention
+        G.linear_wgrad(dx1, sv["attn"], out=self._gw(l, "wo"), **adt)
+        dattn = G.linear_dgrad(dx1, self._w(l, "wo"))
+        dqkv = A.attention_bwd(sv["actx"], dattn)
+        E.rope_(dqkv, S, Hq + Hk, hd, c.rope_theta, inverse=True)
+        G.linear_wgrad(dqkv, sv["h1"], out=self._gw(l, "wqkv"), **adt)
+        dh1 = G.linear_dgrad(dqkv, self._w(l, "wqkv"))
+        dx, _ = E.rmsnorm_bwd(x, self._w(l, "attn_norm"), dh1, c.norm_eps, rstd=sv["rstd1"], dres=dx1,
+                              dw_out=self._gw(l, "attn_norm"), dw_accumulate=acc, dx_out=dh1)
+        return dx
+
+    # -------------------------------------------------------------- protocol
+    def forward(self, ids: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        c, cfg = self.mcfg, self.cfg
+        self._in_backward = False
+        B, S = ids.shape
+        assert S == self.seq_len, f"engine built for seq_len={self.seq_len}, got {S}"
+        self._B = B
+        T = B * S
+        L = c.n_layers
+        acc = self.stage <= 1 and self._micro_in_window > 0
+        with self.timers.phase("forward"):
+            if self.pooled_params:
+                self._ensure_resident(0)
+            ids_flat, labels_flat = ids.reshape(-1), labels.reshape(-1)
+            x = E.embedding_fwd(ids_flat, self.param_view("embed.weight"))
+            ckpts: List[torch.Tensor] = []
+            for l in range(L):
+                if self.pooled_params:
+                    self._ensure_resident(l + 1)
+                    if l + 2 <= L:
+                        self._prefetch(l + 2)
+                ckpts.append(x)
+                x, _ = self._block_fwd(l, x, keep=False)
+            hf, rstd_f, _ = E.rmsnorm_fwd(x, self.param_view("final_norm.weight"), c.norm_eps)
+            # LM head + CE, chunked over tokens; gradients of the head are produced here
+            w_head, g_head = self.param_view("lm_head.weight"), self.grad_view("lm_head.weight")
+            n_valid = (labels_flat >= 0).sum().clamp(min=1).float()
+            dhf = torch.empty_like(hf)
+            loss_tok = torch.empty(T, dtype=torch.float32, device=hf.device)
+            gscale = self.scaler.scale / cfg.grad_accum
+            inv_valid = float(1.0 / n_valid.item()) if not self.on_cuda else None
+            if inv_valid is None:
+                # every token is a target in the packed synthetic/pretraining setting; avoid a host sync
+                inv_valid = 1.0 / T if self._all_valid else float(1.0 / n_valid.item())
+            for ci, t0 in enumerate(range(0, T, self.head_chunk)):
+                t1 = min(T, t0 + self.head_chunk)
+                logits = G.linear_fwd(hf[t0:t1], w_head)
+                loss_tok[t0:t1] = E.cross_entropy_(logits, labels_flat[t0:t1], grad_scale=gscale * inv_valid)
+                G.linear_dgrad(logits, w_head, out=dhf[t0:t1])
+                G.linear_wgrad(logits, hf[t0:t1], out=g_head, accumulate=(acc or ci > 0))
+                del logits
+            loss = loss_tok.sum() * inv_valid
+        self._saved = dict(ids=ids_flat, ckpts=ckpts, x_last=x, rstd_f=rstd_f, dhf=dhf, acc=acc)
+        return loss
+
+    _all_valid = True
+
+    def backward(self, loss: torch.Tensor) -> None:
+        cfg, c = self.cfg, self.mcfg
+        sv = self._saved
+        assert sv is not None, "backward() without a preceding forward()"
+        self._in_backward = True
+        boundary = self.is_gradient_accumulation_boundary()
+        self._reduce_now = self.stage >= 2 or boundary
+        self._reduced = [False] * len(self.layout.units)
+        hook = self.fault_hooks.get("pre_backward")
+        if hook is not None:
+            loss = hook(self, loss)
+        self._loss_accum += loss.detach().float() / cfg.grad_accum
+        acc = sv["acc"]
+        L = c.n_layers
+        with self.timers.phase("backward"):
+            dx, _ = E.rmsnorm_bwd(sv["x_last"], self.param_view("final_norm.weight"), sv["dhf"], c.norm_eps,
+                                  rstd=sv["rstd_f"], dw_out=self.grad_view("final_norm.weight"), dw_accumulate=acc)
+            for l in range(L - 1, -1, -1):
+                ui = l + 1
+                if self.pooled_params:
+                    self._ensure_resident(ui)
+                    if ui - 1 >= 1:
+                        self._prefetch(ui - 1)
+                if self.pooled_grads and self.on_cuda:
+                    evt = self._gslot_free_evt[(ui - 1) % 2]
+                    if evt is not None:
+                        torch.cuda.current_stream().wait_event(evt)
+                dx = self._block_bwd(l, sv["ckpts"][l], dx, acc)
+                sv["ckpts"][l] = None
+                if self._reduce_now:
+                    self._reduce_unit(ui)
+            E.embedding_bwd(sv["ids"], dx, self.grad_view("embed.weight"))
+            if self._reduce_now:
+                self._reduce_unit(0)
+        if self.on_cuda and cfg.overlap_comm:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        hook = self.fault_hooks.get("post_backward")
+        if hook is not None:
+            hook(self)
+        self._saved = None
+        self._micro_in_window = 0 if boundary else self._micro_in_window + 1
+        self._in_backward = False
+
+    def train_step(self, ids: torch.Tensor, labels: torch.Tensor) -> Optional[Dict[str, float]]:
+        loss = self.forward(ids, labels)
+        self.backward(loss)
+        return self.step()

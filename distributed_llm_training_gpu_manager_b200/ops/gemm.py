@@ -28,7 +28,7 @@ def _native(*ts: torch.Tensor) -> bool:
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
-         out: Optional[torch.Tensor] = None, accumulate: bool = False, out_dtype: torch.dtype = torch.bfloat16,
+         out: Optional[torch.Tensor] = None, accumulate: bool = False, out_dtype: Optional[torch.dtype] = None,
          cta_group: int = 0, max_ctas: int = 0) -> torch.Tensor:
     """C[M,N] (+)= A·B. ``a``: [M,K] (or [K,M] if ``a_mn_major``); ``b``: [N,K] (or [K,N] if ``b_mn_major``)."""
     assert a.dim() == 2 and b.dim() == 2
@@ -37,7 +37,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     assert K == Kb, f"reduction dims differ: {K} vs {Kb}"
     if out is None:
         assert not accumulate, "accumulate=True needs an existing output"
-        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+        out = torch.empty((M, N), dtype=out_dtype or a.dtype, device=a.device)
     else:
         assert out.shape == (M, N) and out.stride(1) == 1
         out_dtype = out.dtype
@@ -73,5 +73,5 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] 
 
 
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False,
-                 out_dtype: torch.dtype = torch.bfloat16, **kw) -> torch.Tensor:
+                 out_dtype: Optional[torch.dtype] = None, **kw) -> torch.Tensor:
     return gemm(dy, x, a_mn_major=True, b_mn_major=True, out=out, accumulate=accumulate, out_dtype=out_dtype, **kw)
