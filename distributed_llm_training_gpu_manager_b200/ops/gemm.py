@@ -37,7 +37,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     assert K == Kb, f"reduction dims differ: {K} vs {Kb}"
     if out is None:
         assert not accumulate, "accumulate=True needs an existing output"
-        out = torch.empty((M, N), dtype=out_dtype or a.dtype, device=a.device)
+        out_dtype = out_dtype or a.dtype
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
     else:
         assert out.shape == (M, N) and out.stride(1) == 1
         out_dtype = out.dtype

@@ -50,6 +50,21 @@ _SIGNATURES = {
     "bz_clip_coef": (i32, [vp, f32, f32, vp, vp, vp, vp]),
     "bz_cast_f32_to_bf16": (i32, [vp, vp, i64, vp]),
     "bz_cast_bf16_to_f32": (i32, [vp, vp, i64, vp]),
+    "bz_comm_max_world": (i32, []),
+    "bz_comm_signal_pad_bytes": (i32, []),
+    "bz_comm_segment_bytes": (i32, []),
+    "bz_fused_comm_workspace_bytes": (i32, []),
+    "bz_symm_alloc": (i32, [u64, C.POINTER(vp)]),
+    "bz_symm_free": (i32, [vp]),
+    "bz_ipc_export": (i32, [vp, C.c_char_p]),
+    "bz_ipc_import": (i32, [C.c_char_p, C.POINTER(vp)]),
+    "bz_ipc_close": (i32, [vp]),
+    "bz_enable_peer_access": (i32, [i32]),
+    "bz_fused_reduce_scatter": (i32, [C.POINTER(vp), C.POINTER(vp), vp, i32, vp, i32, f32, vp, vp, vp, vp, C.c_uint,
+                                      i32, i32, i32, i32, i32, vp]),
+    "bz_fused_adam_push": (i32, [C.POINTER(vp), C.POINTER(vp), vp, i32, vp, vp, vp, vp, i32, vp, f32, f32, f32, f32,
+                                 f32, i32, vp, vp, vp, C.c_uint, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "bz_pull_allgather": (i32, [C.POINTER(vp), vp, i32, vp, i32, i32, i32, vp]),
 }
 
 

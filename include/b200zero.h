@@ -99,6 +99,50 @@ int bz_clip_coef(const float* sumsq, float max_norm, float extra_scale, float* c
 int bz_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
 int bz_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream);
 
+/* ---- H2: peer-memory runtime (CUDA IPC; one process per GPU) --------------------
+ * bz_symm_alloc: zero-filled device allocation suitable for IPC export (cudaMalloc —
+ * set-up time only). Handles are 64 opaque bytes exchanged out of band
+ * (torch.distributed all_gather in parallel/symm.py). New scope: the reference has no
+ * communication backend at all. */
+int bz_comm_max_world(void);
+int bz_comm_signal_pad_bytes(void);
+int bz_comm_segment_bytes(void);
+int bz_fused_comm_workspace_bytes(void);
+int bz_symm_alloc(unsigned long long bytes, void** out);
+int bz_symm_free(void* p);
+int bz_ipc_export(void* p, unsigned char* handle64);
+int bz_ipc_import(const unsigned char* handle64, void** out);
+int bz_ipc_close(void* p);
+int bz_enable_peer_access(int peer_device);
+
+/* ---- K1: fused reduce-scatter + scale + accumulate + ‖g‖² + isfinite ---------------
+ * Segment record (bz_comm_segment_bytes() = 32 bytes): {int64 full_off, int64 numel,
+ * int64 shard_off, int32 partitioned, int32 pad}; element offsets, multiples of 16.
+ * grad_ptrs[ws] / signal_ptrs[ws]: peer-mapped pointers, index = rank. workspace:
+ * bz_fused_comm_workspace_bytes() bytes, zeroed once. epoch must increase by one per
+ * call per channel on every rank. use_barrier=0 skips the cross-rank flags (single-GPU
+ * emulation of several ranks: never run mutually-waiting kernels on one device).
+ * Replaces ncclReduceScatter + cast + norm + isfinite (SURVEY.md §2.3 X1,X4,X5,X6,F9). */
+int bz_fused_reduce_scatter(void* const* grad_ptrs, void* const* signal_ptrs, const void* segs, int nseg,
+                            void* shard_grads, int shard_is_f32, float scale, float* workspace, float* sumsq_part,
+                            float* sumsq_repl, int* nonfinite_flag, unsigned int epoch, int channel, int rank, int ws,
+                            int use_barrier, int ctas, void* stream);
+
+/* ---- K3: AdamW on the shard + push all-gather of the updated bf16 rows -------------
+ * push=1: rows are stored into every rank's gathered parameter buffer (param_ptrs);
+ * shard_params (optional) receives the local bf16 copy. Predicated on *skip_flag.
+ * Replaces FusedAdam + cast + ncclAllGather (SURVEY.md §2.3 F7,F10,X3). */
+int bz_fused_adam_push(void* const* param_ptrs, void* const* signal_ptrs, const void* segs, int nseg, float* master,
+                       float* m, float* v, void* shard_grads, int grads_are_f32, void* shard_params, float lr,
+                       float beta1, float beta2, float eps, float weight_decay, int step,
+                       const float* grad_scale_dev, const int* skip_flag, float* workspace, unsigned int epoch,
+                       int channel, int rank, int ws, int push, int use_barrier, int zero_grads, int ctas,
+                       void* stream);
+
+/* ---- pull all-gather of a unit's rows from every peer's shard (ZeRO-3, X2) ---------- */
+int bz_pull_allgather(void* const* shard_param_ptrs, const void* segs, int nseg, void* dst_unit, int rank, int ws,
+                      int ctas, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
