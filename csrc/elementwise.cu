@@ -537,3 +537,89 @@ extern "C" int bz_add_bf16(const void* a, const void* b, void* out, long long n,
   BZ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
+
+// =====================================================================================
+// RMSNorm backward without caller-provided scratch.
+//
+// Who this is for: callers that are not allowed to allocate device memory when they need the
+// backward pass. Three real cases: (1) a step loop that must not stall — cudaMalloc and cudaFree
+// synchronise the whole device, so an allocation in the middle of a step serialises every stream
+// that is overlapping copies and collectives with compute; (2) a job whose HBM is planned to the
+// last block (ZeRO-3 at 70B sizing): there is no slack to allocate from, and a failed allocation
+// mid-step would kill the run; (3) plain C/C++ hosts that link this library without PyTorch and
+// therefore have no caching allocator to carve a workspace from.
+//
+// bz_rmsnorm_bwd needs `grid x D` floats of scratch for the per-CTA dw partial sums. Here that
+// scratch lives in the library itself: a file-scope device array of
+// BZ_RMSNORM_BWD_STATIC_SCRATCH_FLOATS floats (5 MiB), present on every GPU that loads the
+// library until the process exits. Launch geometry is identical to bz_rmsnorm_bwd, so the two
+// produce the same bits.
+//
+// Rules for the caller:
+//  * Problems whose partial sums do not fit (min(T, 2*SMs) * D floats > capacity) are refused
+//    with an error; use bz_rmsnorm_bwd with your own workspace for those.
+//  * The FIRST call on each device looks up the array's device address
+//    (cudaGetSymbolAddress, with that device current). Make that first call during set-up,
+//    before any stream capture begins. Later calls on that device only launch kernels.
+//  * All calls on a device share the one array. Calls whose kernels can overlap on the GPU
+//    (different streams without an ordering between them) race on it; keep them on one stream
+//    or order them with events. The array keeps whatever the previous call left in it; that is
+//    harmless here because every slot the reduction pass reads is written by the partial pass of
+//    the same call — nothing relies on the scratch starting at zero.
+//  * No cudaMalloc / cudaFree / allocating library routine is called, on any call.
+// =====================================================================================
+namespace bz {
+
+constexpr int kStaticScratchFloats = BZ_RMSNORM_BWD_STATIC_SCRATCH_FLOATS;
+static __device__ __align__(256) float g_rmsnorm_bwd_scratch[kStaticScratchFloats];
+
+// Device address of g_rmsnorm_bwd_scratch per device ordinal. In host code the symbol name is only
+// a stand-in; the address a kernel may dereference has to come from cudaGetSymbolAddress.
+static float* g_scratch_addr[64] = {nullptr};
+
+static int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  BZ_CUDA_CHECK(cudaGetDevice(&dev));
+  BZ_REQUIRE(dev >= 0 && dev < 64, "rmsnorm_bwd_static_scratch: device ordinal %d out of range", dev);
+  if (g_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    BZ_CUDA_CHECK(cudaGetSymbolAddress(&p, g_rmsnorm_bwd_scratch));
+    BZ_REQUIRE(p != nullptr, "rmsnorm_bwd_static_scratch: cudaGetSymbolAddress returned a null address");
+    g_scratch_addr[dev] = static_cast<float*>(p);
+  }
+  *out = g_scratch_addr[dev];
+  return 0;
+}
+
+}  // namespace bz
+
+extern "C" int bz_rmsnorm_bwd_static_scratch(const void* x, const void* w, const float* rstd, const void* dy,
+                                             const void* dres, void* dx, void* dw, int dw_is_f32, int dw_accumulate,
+                                             int T, int D, float eps, void* stream) {
+  BZ_REQUIRE(D % 8 == 0, "rmsnorm_bwd_static_scratch: D=%d must be a multiple of 8", D);
+  const int vpt = vpt_for(D);
+  BZ_REQUIRE(vpt != 0, "rmsnorm_bwd_static_scratch: D=%d too large", D);
+  if (T <= 0) return 0;
+  const int grid = min(T, device_sm_count() * 2);  // same geometry as bz_rmsnorm_bwd
+  const long long need = (long long)grid * D;
+  BZ_REQUIRE(dw == nullptr || need <= (long long)kStaticScratchFloats,
+             "rmsnorm_bwd_static_scratch: T=%d D=%d needs %lld floats of scratch but the built-in scratch holds %d; "
+             "call bz_rmsnorm_bwd with a caller-provided workspace instead",
+             T, D, need, kStaticScratchFloats);
+  float* part = nullptr;
+  if (dw != nullptr) {
+    if (int rc = static_scratch_for_current_device(&part)) return rc;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  auto X = (const __nv_bfloat16*)x; auto W = (const __nv_bfloat16*)w; auto DY = (const __nv_bfloat16*)dy;
+  auto DR = (const __nv_bfloat16*)dres; auto DX = (__nv_bfloat16*)dx;
+  if (vpt == 1) rmsnorm_bwd_kernel<1><<<grid, EW_THREADS, 0, st>>>(X, W, rstd, DY, DR, DX, part, T, D, eps);
+  else if (vpt == 2) rmsnorm_bwd_kernel<2><<<grid, EW_THREADS, 0, st>>>(X, W, rstd, DY, DR, DX, part, T, D, eps);
+  else rmsnorm_bwd_kernel<4><<<grid, EW_THREADS, 0, st>>>(X, W, rstd, DY, DR, DX, part, T, D, eps);
+  BZ_CUDA_CHECK(cudaGetLastError());
+  if (dw != nullptr) {
+    rmsnorm_dw_reduce_kernel<<<(D + 255) / 256, 256, 0, st>>>(part, grid, D, dw, dw_is_f32, dw_accumulate);
+    BZ_CUDA_CHECK(cudaGetLastError());
+  }
+  return 0;
+}

@@ -54,6 +54,21 @@ int bz_rmsnorm_bwd(const void* x, const void* w, const float* rstd, const void* 
                    void* dw, int dw_is_f32, int dw_accumulate, float* workspace, int T, int D, float eps,
                    void* stream);
 
+/* RMSNorm backward for callers that may not allocate (no counterpart in the reference, which has
+ * no kernels). Same maths, launch geometry and results as bz_rmsnorm_bwd, but the dw partial-sum
+ * scratch is a device array built into the library (BZ_RMSNORM_BWD_STATIC_SCRATCH_FLOATS floats,
+ * 5 MiB per GPU for the life of the process) instead of a caller workspace. Meant for step loops
+ * that must not hit cudaMalloc's device-wide synchronisation, jobs with no HBM slack left, and
+ * C/C++ hosts without an allocator to lend a workspace. Refuses problems needing more than the
+ * built-in scratch (min(T, 2*SMs)*D floats). The first call on each device resolves the array's
+ * address — make it during set-up, before any stream capture. All calls on a device share the
+ * array: calls that can overlap on the GPU race; serialise them on one stream or with events.
+ * Never calls cudaMalloc/cudaFree. */
+#define BZ_RMSNORM_BWD_STATIC_SCRATCH_FLOATS 1310720
+int bz_rmsnorm_bwd_static_scratch(const void* x, const void* w, const float* rstd, const void* dy, const void* dres,
+                                  void* dx, void* dw, int dw_is_f32, int dw_accumulate, int T, int D, float eps,
+                                  void* stream);
+
 /* ---- K7: RoPE, in place on the first n_rot_heads heads of each row --------
  * cos/sin: fp32 [S, head_dim/2]; position = row % S; inverse=1 applies the
  * transpose rotation (backward). */
