@@ -66,6 +66,8 @@ class FaultPlan:
             step = eng.global_steps + 1
             if plan.nan_grad_at == step and plan._once(f"nan{step}"):
                 eng.shard_grads[0] = float("nan")
+                if getattr(eng, "fused", None) is not None:   # the fused path derives the flag inside its reduce kernels
+                    eng._flag.fill_(1)
 
         engine.fault_hooks["pre_backward"] = pre_backward
         engine.fault_hooks["post_backward"] = post_backward

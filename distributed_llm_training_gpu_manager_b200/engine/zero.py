@@ -146,6 +146,9 @@ class ZeroEngine:
         self.last_metrics: Dict[str, float] = {}
         self.fault_hooks: Dict[str, Callable] = {}
         self.fused = None
+        self._symm: Dict[str, Any] = {}
+        self._want_fused = (comm == "fused" and self.on_cuda and self.world_size > 1
+                            and self.cfg.compute_dtype == torch.bfloat16)
         self._in_backward = False
         self._reduce_now = True
         self._prefetch_evt: Dict[int, Any] = {}
@@ -184,8 +187,11 @@ class ZeroEngine:
         if self.comm_mode == "auto":
             self.comm_mode = "nccl" if self.on_cuda else "gloo"
         if self.comm_mode == "fused":
-            from ..parallel.fused import FusedComm
-            self.fused = FusedComm(self)
+            if self._want_fused:
+                from ..parallel.fused import FusedComm
+                self.fused = FusedComm(self)
+            else:
+                self.comm_mode = "nccl" if self.on_cuda else "gloo"  # single rank / CPU: nothing to fuse
 
     # ------------------------------------------------------------------ buffers
     def _slice_rows(self, spec: ParamSpec, full: torch.Tensor) -> torch.Tensor:
@@ -193,6 +199,13 @@ class ZeroEngine:
             return full.reshape(-1)
         rows = spec.shape[0] // self.world_size
         return full[self.rank * rows:(self.rank + 1) * rows].reshape(-1)
+
+    def _zeros(self, numel: int, dtype: torch.dtype, name: str, symmetric: bool = False) -> torch.Tensor:
+        """Device buffer; peer-mapped (CUDA IPC) when the fused backend will touch it from other ranks."""
+        if symmetric and self._want_fused:
+            from ..parallel.fused import FusedComm
+            return FusedComm.alloc(self, numel, dtype, name)
+        return torch.zeros(numel, dtype=dtype, device=self.device)
 
     def _build_buffers(self) -> None:
         L, cfg, dev, cd = self.layout, self.cfg, self.device, self.compute_dtype
@@ -202,7 +215,7 @@ class ZeroEngine:
         self.master, self.exp_avg, self.exp_avg_sq = mk(), mk(), mk()
         self.state_device = state_dev
         self.shard_grads = torch.zeros(L.shard_numel, dtype=cfg.accum_dtype, device=dev)
-        self.shard_params = torch.zeros(L.shard_numel, dtype=cd, device=dev)
+        self.shard_params = self._zeros(L.shard_numel, cd, "shard_params", symmetric=self.stage >= 3)
         # master <- initial fp32 values, own rows only
         for u in L.units:
             for spec in u.params:
@@ -225,7 +238,7 @@ class ZeroEngine:
             self._slot_owner: List[Optional[int]] = [None, None]
         else:
             total = sum(u.full_numel for u in L.units)
-            self._pbuf_all = torch.zeros(total, dtype=cd, device=dev)
+            self._pbuf_all = self._zeros(total, cd, "pbuf_all", symmetric=True)
             off, self._unit_pbuf = 0, []
             for u in L.units:
                 self._unit_pbuf.append(self._pbuf_all[off:off + u.full_numel])
@@ -236,12 +249,12 @@ class ZeroEngine:
         self.pooled_grads = self.stage >= 2 and nblk >= 2
         if self.pooled_grads:
             blk_numel = max(u.full_numel for u in L.units[1:])
-            self._gbuf_root = torch.zeros(L.units[0].full_numel, dtype=cd, device=dev)
-            self._gbuf_blk = [torch.zeros(blk_numel, dtype=cd, device=dev) for _ in range(2)]
+            self._gbuf_root = self._zeros(L.units[0].full_numel, cd, "gbuf_root", symmetric=True)
+            self._gbuf_blk = [self._zeros(blk_numel, cd, f"gbuf_blk{i}", symmetric=True) for i in range(2)]
             self._unit_gbuf = [self._gbuf_root] + [self._gbuf_blk[(i - 1) % 2] for i in range(1, len(L.units))]
         else:
             total = sum(u.full_numel for u in L.units)
-            self._gbuf_all = torch.zeros(total, dtype=cd, device=dev)
+            self._gbuf_all = self._zeros(total, cd, "gbuf_all", symmetric=True)
             off, self._unit_gbuf = 0, []
             for u in L.units:
                 self._unit_gbuf.append(self._gbuf_all[off:off + u.full_numel])
@@ -426,6 +439,8 @@ class ZeroEngine:
         self._reduce_now = self.stage >= 2 or boundary
         self._pending = list(self._need)
         self._reduced = [False] * len(self.layout.units)
+        if self.fused is not None:
+            self.fused.begin_micro_step()
         hook = self.fault_hooks.get("pre_backward")
         if hook is not None:
             loss = hook(self, loss)
@@ -456,12 +471,15 @@ class ZeroEngine:
     def _optimizer_step(self) -> Dict[str, float]:
         cfg, L = self.cfg, self.layout
         with self.timers.phase("step"):
-            self._flag.zero_()
             st = self._stats
             st.zero_()
-            O.sumsq(self.shard_grads[:L.part_numel], st[0:1], nonfinite_flag=self._flag) if L.part_numel else None
-            if L.shard_numel > L.part_numel:
-                O.sumsq(self.shard_grads[L.part_numel:], st[3:4], nonfinite_flag=self._flag)
+            if self.fused is not None:       # Σg² and the flag came out of the reduce-scatter kernels
+                st[0] = self.fused.sumsq_part[0]
+                st[3] = self.fused.sumsq_repl[0]
+            else:
+                O.sumsq(self.shard_grads[:L.part_numel], st[0:1], nonfinite_flag=self._flag) if L.part_numel else None
+                if L.shard_numel > L.part_numel:
+                    O.sumsq(self.shard_grads[L.part_numel:], st[3:4], nonfinite_flag=self._flag)
             st[1] = self._flag.float()[0]
             st[2] = self._loss_accum[0] / self.world_size
             if self.world_size > 1:
@@ -476,7 +494,9 @@ class ZeroEngine:
                         self._coef, self._norm, self._flag)
             lr = self.schedule.lr_at(self.global_steps)
             step_no = self.global_steps - self.skipped_steps + 1
-            if self.state_device.type == "cpu" and self.on_cuda:
+            if self.fused is not None:
+                self.fused.adam_and_publish(lr, step_no)
+            elif self.state_device.type == "cpu" and self.on_cuda:
                 self._offloaded_adam(lr, step_no)
             else:
                 O.adamw_step(self.master, self.exp_avg, self.exp_avg_sq, self.shard_grads, lr=lr, beta1=cfg.betas[0],
@@ -485,7 +505,8 @@ class ZeroEngine:
                              param_out=self.shard_params if self.compute_dtype == torch.bfloat16 and self.on_cuda else None)
                 if not (self.compute_dtype == torch.bfloat16 and self.on_cuda):
                     self.shard_params.copy_(self.master.to(self.compute_dtype))
-            self.shard_grads.zero_()
+            if self.fused is None:
+                self.shard_grads.zero_()       # (the fused Adam kernel zeroes the shard as it reads it)
             # host read: the one sync of the step (feeds the loss monitor)
             if self.on_cuda:
                 self._stats_host.copy_(torch.stack([self._sumsq[0], self._flag[0].float(), st[2], self._norm[0] * inv_scale]),
@@ -494,6 +515,7 @@ class ZeroEngine:
                 vals = self._stats_host.tolist()
             else:
                 vals = [float(self._sumsq[0]), float(self._flag[0]), float(st[2]), float(self._norm[0]) * inv_scale]
+            self._flag.zero_()                 # clean for the next step's reduce / norm kernels
             overflow = vals[1] > 0
             self.scaler.update(overflow)
             if overflow:
@@ -504,6 +526,8 @@ class ZeroEngine:
                     self._resident = [False] * len(L.units)
                     self._slot_owner = [None, None]
                     self._gather_unit(0)
+                elif self.fused is not None:
+                    pass                        # rows were pushed into every rank's buffers by the Adam kernel
                 else:
                     for ui in range(len(L.units)):
                         self._gather_unit(ui)

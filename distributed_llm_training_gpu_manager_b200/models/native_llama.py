@@ -205,6 +205,8 @@ class NativeLlamaEngine(ZeroEngine):
         boundary = self.is_gradient_accumulation_boundary()
         self._reduce_now = self.stage >= 2 or boundary
         self._reduced = [False] * len(self.layout.units)
+        if self.fused is not None:
+            self.fused.begin_micro_step()
         hook = self.fault_hooks.get("pre_backward")
         if hook is not None:
             loss = hook(self, loss)

@@ -1,0 +1,134 @@
+"""Fused-collective backend for :class:`ZeroEngine` (``comm="fused"``): the per-unit gradient
+reduce-scatter (K1) and the optimizer step with push all-gather (K3) run as our own kernels over
+peer-mapped memory instead of NCCL calls; ZeRO-3 weight gathers use the pull all-gather kernel
+(and the all-gather→GEMM kernel K2 for the block's first GEMM, see ``ops/ag_gemm.py``).
+
+Division of labour per optimizer step (cf. ``engine/zero.py`` which does the same with NCCL):
+
+    backward, unit u done ──► bz_fused_reduce_scatter(u): pull my rows from all peers, fp32 sum in
+                              rank order, ×1/ws, += shard, Σg² partials, non-finite flag
+    after the last unit   ──► one 3-float NCCL all-reduce (Σ‖g‖², flag, loss) — 12 bytes, control only
+    then                  ──► bz_fused_adam_push: AdamW on the shard (skip if flag; ×clip coef read
+                              on device) and, for stage ≤ 2, store the new bf16 rows into every
+                              peer's parameter buffer; epoch barrier so nobody reads early
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import torch
+
+from ..ops import lib as _lib
+from .symm import SymmetricBuffer
+
+RS_CHANNEL, ADAM_CHANNEL = 0, 1
+
+
+def segment_table(records: List[tuple], device) -> torch.Tensor:
+    """records: (full_off, numel, shard_off, partitioned) -> int64 [n, 4] device tensor whose rows
+    are the 32-byte Segment structs of csrc/fused_comm.cu."""
+    rows = [[fo, n, so, int(bool(part))] for fo, n, so, part in records]   # int32 partitioned + int32 pad = 1 int64 (LE)
+    return torch.tensor(rows, dtype=torch.int64, device=device).contiguous()
+
+
+class FusedComm:
+    def __init__(self, engine, rs_ctas: int = 48, adam_ctas: int = 148):
+        assert engine.on_cuda, "fused communication needs GPUs"
+        self.e = engine
+        self.L = _lib.load(required=True)
+        assert engine.world_size <= self.L.bz_comm_max_world()
+        assert engine.compute_dtype == torch.bfloat16, "fused kernels reduce bf16 gradients"
+        self.rs_ctas, self.adam_ctas = rs_ctas, adam_ctas
+        dev = engine.device
+        self.signal = SymmetricBuffer(self.L.bz_comm_signal_pad_bytes(), device=dev)
+        self.workspace = torch.zeros(self.L.bz_fused_comm_workspace_bytes() // 4, dtype=torch.float32, device=dev)
+        self.sumsq_part = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.sumsq_repl = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.epoch = {RS_CHANNEL: 0, ADAM_CHANNEL: 0}
+        self._sig_ptrs = self.signal.ptr_array()
+        L = engine.layout
+        # per-unit segment tables (offsets relative to the unit's buffer)
+        self._unit_segs: Dict[int, torch.Tensor] = {}
+        for u in L.units:
+            self._unit_segs[u.index] = segment_table(
+                [(s.full_offset, s.numel, s.shard_offset, s.partitioned) for s in u.params], dev)
+        self.launches = 0
+
+    # -- symmetric buffers are created by the engine through this hook --------------------------------
+    @staticmethod
+    def alloc(engine, numel: int, dtype: torch.dtype, name: str) -> torch.Tensor:
+        es = torch.empty((), dtype=dtype).element_size()
+        buf = SymmetricBuffer(numel * es, device=engine.device)
+        engine._symm[name] = buf
+        return buf.tensor(dtype, numel)
+
+    def _ptrs_for(self, tensor: torch.Tensor):
+        """Peer pointer array for a tensor living inside one of the engine's symmetric buffers."""
+        p = tensor.data_ptr()
+        for buf in self.e._symm.values():
+            if buf.local_ptr <= p < buf.local_ptr + buf.nbytes:
+                return buf.ptr_array(p - buf.local_ptr)
+        raise RuntimeError("tensor is not in symmetric memory")
+
+    # -- K1 ------------------------------------------------------------------------------------
+    def begin_micro_step(self) -> None:
+        self.sumsq_part.zero_()
+        self.sumsq_repl.zero_()
+
+    def reduce_unit(self, ui: int, scale: float) -> bool:
+        e = self.e
+        gb = e._unit_gbuf[ui]
+        self.epoch[RS_CHANNEL] += 1
+        rc = self.L.bz_fused_reduce_scatter(
+            self._ptrs_for(gb), self._sig_ptrs, self._unit_segs[ui].data_ptr(), len(e.layout.units[ui].params),
+            e.shard_grads.data_ptr(), int(e.shard_grads.dtype == torch.float32), scale, self.workspace.data_ptr(),
+            self.sumsq_part.data_ptr(), self.sumsq_repl.data_ptr(), e._flag.data_ptr(), self.epoch[RS_CHANNEL],
+            RS_CHANNEL, e.rank, e.world_size, 1, self.rs_ctas, _lib.stream())
+        _lib.check(rc, "fused_reduce_scatter")
+        _lib.add_launches(1)
+        return True
+
+    # -- ZeRO-3 gather -------------------------------------------------------------------------
+    def gather_unit(self, ui: int) -> bool:
+        e = self.e
+        if e.stage < 3 or "shard_params" not in e._symm:
+            return False
+        rc = self.L.bz_pull_allgather(self._ptrs_for(e.shard_params), self._unit_segs[ui].data_ptr(),
+                                      len(e.layout.units[ui].params), e._unit_pbuf[ui].data_ptr(), e.rank,
+                                      e.world_size, self.rs_ctas, _lib.stream())
+        _lib.check(rc, "pull_allgather")
+        return True
+
+    # -- K3 ------------------------------------------------------------------------------------
+    def adam_and_publish(self, lr: float, step_no: int) -> None:
+        e, cfg = self.e, self.e.cfg
+        push = int(e.stage <= 2)
+        self.epoch[ADAM_CHANNEL] += 1
+        if push:
+            if not hasattr(self, "_all_segs"):
+                recs, off = [], 0
+                for u in e.layout.units:
+                    recs += [(off + s.full_offset, s.numel, s.shard_offset, s.partitioned) for s in u.params]
+                    off += u.full_numel
+                self._all_segs = segment_table(recs, e.device)
+                self._all_ptrs = self._ptrs_for(e._pbuf_all)
+            segs, nseg, pptrs = self._all_segs, self._all_segs.shape[0], self._all_ptrs
+        else:
+            if not hasattr(self, "_all_segs"):
+                recs = [(0, s.numel, s.shard_offset, s.partitioned) for u in e.layout.units for s in u.params]
+                self._all_segs = segment_table(recs, e.device)
+            segs, nseg, pptrs = self._all_segs, self._all_segs.shape[0], None
+        rc = self.L.bz_fused_adam_push(
+            pptrs, self._sig_ptrs, segs.data_ptr(), nseg, e.master.data_ptr(), e.exp_avg.data_ptr(),
+            e.exp_avg_sq.data_ptr(), e.shard_grads.data_ptr(), int(e.shard_grads.dtype == torch.float32),
+            e.shard_params.data_ptr(), lr, cfg.betas[0], cfg.betas[1], cfg.eps, cfg.weight_decay, step_no,
+            e._coef.data_ptr(), e._flag.data_ptr(), self.workspace.data_ptr(), self.epoch[ADAM_CHANNEL], ADAM_CHANNEL,
+            e.rank, e.world_size, push, 1, 1, self.adam_ctas, _lib.stream())
+        _lib.check(rc, "fused_adam_push")
+
+    def close(self) -> None:
+        self.signal.close()
+        for b in self.e._symm.values():
+            b.close()
+        self.e._symm.clear()

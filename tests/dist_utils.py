@@ -48,3 +48,40 @@ def run_ranks(fn, world: int = 2, args=()):
         status, payload = results[r]
         assert status == "ok", f"rank {r} failed:\n{payload}"
     return [results[r][1] for r in range(world)]
+
+
+def _entry_nccl(rank, world, port, fn, args, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    try:
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        out = fn(rank, world, *args)
+        ret[rank] = ("ok", out)
+    except BaseException:
+        ret[rank] = ("err", traceback.format_exc())
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def run_ranks_nccl(fn, world: int, args=()):
+    """One process per GPU over NCCL on this node."""
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = free_port()
+        procs = [ctx.Process(target=_entry_nccl, args=(r, world, port, fn, args, ret)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(900)
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+        results = dict(ret)
+    for r in range(world):
+        assert r in results, f"rank {r} produced no result (crashed or timed out)"
+        status, payload = results[r]
+        assert status == "ok", f"rank {r} failed:\n{payload}"
+    return [results[r][1] for r in range(world)]
