@@ -24,7 +24,7 @@
 namespace bz {
 
 constexpr int MAX_WS = 8;
-constexpr int COMM_THREADS = 512;
+constexpr int COMM_THREADS = 256;  // small footprint: must co-reside with a persistent GEMM CTA on the same SM
 constexpr int SIG_CHANNELS = 8;
 constexpr int SIG_PHASES = 3;  // 0: data ready, 1: done reading, 2: pushed
 
@@ -279,8 +279,9 @@ fused_adam_push_kernel(const __grid_constant__ PeerTable pt, const Segment* __re
       }
     }
   }
-  if (push && use_barrier) {
-    // phase 2: everyone's rows have landed everywhere before any rank's next forward may start
+  if (use_barrier) {
+    // phase 2: every rank's rows are final (and, when pushing, have landed everywhere) before any
+    // rank's next gather / forward may read them
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();
@@ -314,12 +315,29 @@ pull_allgather_kernel(const __grid_constant__ PeerTable pt, const Segment* __res
     const long long n = sg.numel / ws;
     const long long nvec = n >> 3;
     const long long total = nvec * ws;
-    for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < total; j += (long long)gridDim.x * blockDim.x) {
-      // interleave peers so that all NVLink ports are busy at once; start at our own neighbour
-      const int p = (int)((j + rank) % ws);
-      const long long i = j / ws;
-      const uint4 val = ld_peer_v4(reinterpret_cast<const __nv_bfloat16*>(pt.data[p]) + sg.shard_off + i * 8);
-      *reinterpret_cast<uint4*>(dst_unit + sg.full_off + (long long)p * n + i * 8) = val;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    constexpr int UNR = 4;  // four 128-bit peer loads in flight per thread
+    for (long long j0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; j0 < total; j0 += stride * UNR) {
+      uint4 val[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const long long j = j0 + u * stride;
+        if (j < total) {
+          // interleave peers so that all NVLink ports are busy at once; start at our own neighbour
+          const int p = (int)((j + rank) % ws);
+          const long long i = j / ws;
+          val[u] = ld_peer_v4(reinterpret_cast<const __nv_bfloat16*>(pt.data[p]) + sg.shard_off + i * 8);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const long long j = j0 + u * stride;
+        if (j < total) {
+          const int p = (int)((j + rank) % ws);
+          const long long i = j / ws;
+          *reinterpret_cast<uint4*>(dst_unit + sg.full_off + (long long)p * n + i * 8) = val[u];
+        }
+      }
     }
   }
 }

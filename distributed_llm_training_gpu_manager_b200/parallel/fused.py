@@ -33,7 +33,12 @@ def segment_table(records: List[tuple], device) -> torch.Tensor:
 
 
 class FusedComm:
-    def __init__(self, engine, rs_ctas: int = 48, adam_ctas: int = 148):
+    def __init__(self, engine, rs_ctas: Optional[int] = None, adam_ctas: Optional[int] = None):
+        import os
+        rs_ctas = rs_ctas or int(os.environ.get("B200ZERO_RS_CTAS", "128"))
+        adam_ctas = adam_ctas or int(os.environ.get("B200ZERO_ADAM_CTAS", "148"))
+        self.use_fused_gather = os.environ.get("B200ZERO_FUSED_GATHER", "1") == "1"
+        self.use_fused_rs = os.environ.get("B200ZERO_FUSED_RS", "1") == "1"
         assert engine.on_cuda, "fused communication needs GPUs"
         self.e = engine
         self.L = _lib.load(required=True)
@@ -78,6 +83,8 @@ class FusedComm:
 
     def reduce_unit(self, ui: int, scale: float) -> bool:
         e = self.e
+        if not self.use_fused_rs:
+            return False
         gb = e._unit_gbuf[ui]
         self.epoch[RS_CHANNEL] += 1
         rc = self.L.bz_fused_reduce_scatter(
@@ -92,7 +99,7 @@ class FusedComm:
     # -- ZeRO-3 gather -------------------------------------------------------------------------
     def gather_unit(self, ui: int) -> bool:
         e = self.e
-        if e.stage < 3 or "shard_params" not in e._symm:
+        if e.stage < 3 or "shard_params" not in e._symm or not self.use_fused_gather:
             return False
         rc = self.L.bz_pull_allgather(self._ptrs_for(e.shard_params), self._unit_segs[ui].data_ptr(),
                                       len(e.layout.units[ui].params), e._unit_pbuf[ui].data_ptr(), e.rank,

@@ -158,6 +158,13 @@ int bz_fused_adam_push(void* const* param_ptrs, void* const* signal_ptrs, const 
 int bz_pull_allgather(void* const* shard_param_ptrs, const void* segs, int nseg, void* dst_unit, int rank, int ws,
                       int ctas, void* stream);
 
+/* ---- K6: causal flash attention forward (head_dim 128, GQA) on tcgen05 -----------
+ * qkv: fused [B*S, (Hq+2*Hkv)*128] bf16 with RoPE applied; out: [B*S, Hq*128] bf16;
+ * lse (optional): [Hq, B*S] fp32 natural-log-sum-exp of the scaled scores.
+ * S % 128 == 0. */
+int bz_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int Hq, int Hk, int head_dim,
+                      float softmax_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
