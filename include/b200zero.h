@@ -165,6 +165,16 @@ int bz_pull_allgather(void* const* shard_param_ptrs, const void* segs, int nseg,
 int bz_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int Hq, int Hk, int head_dim,
                       float softmax_scale, void* stream);
 
+/* ---- K2: all-gather -> GEMM in one kernel ------------------------------------------
+ * Y[M,N] = X[M,K] · W[N,K]^T with W row-partitioned over `ws` ranks. shard_ptrs[p] is
+ * rank p's [N/ws, K] slice (peer-mapped; entry `rank` local). Communication warps in
+ * every CTA pull W chunk by chunk over NVLink and write it through to Wfull [N,K];
+ * GEMM tiles consume chunks as they arrive. chunk_ready: >= ceil(N/256) uint32 scratch.
+ * Replaces ncclAllGather + cuBLAS GEMM (SURVEY.md §2.3 X2 + F1). */
+int bz_ag_gemm_max_tiles(void);
+int bz_ag_gemm_bf16(const void* X, void* const* shard_ptrs, void* Wfull, void* Y, void* chunk_ready, int M, int N,
+                    int K, int ldx, int ldc, int rank, int ws, int cta_group, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
