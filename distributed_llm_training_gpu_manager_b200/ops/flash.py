@@ -24,6 +24,30 @@ def flash_fwd(qkv: torch.Tensor, B: int, S: int, Hq: int, Hk: int, hd: int,
     return out, lse
 
 
+_lib.register("bz_flash_attn_bwd_workspace_floats", _lib.i64, [_lib.i32, _lib.i32, _lib.i32])
+_lib.register("bz_flash_attn_bwd", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.i32, _lib.i32,
+                                              _lib.i32, _lib.i32, _lib.i32, _lib.f32, _lib.vp])
+_ws = {}
+
+
+def flash_bwd(qkv: torch.Tensor, out: torch.Tensor, lse: torch.Tensor, dout: torch.Tensor, B: int, S: int, Hq: int,
+              Hk: int, hd: int, dqkv: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Gradient w.r.t. the fused QKV buffer (same layout as ``qkv``)."""
+    T = B * S
+    L = _lib.load(required=True)
+    if dqkv is None:
+        dqkv = torch.empty_like(qkv)
+    need = L.bz_flash_attn_bwd_workspace_floats(B, S, Hq)
+    key = str(qkv.device)
+    if key not in _ws or _ws[key].numel() < need:
+        _ws[key] = torch.empty(need, dtype=torch.float32, device=qkv.device)
+    assert dout.is_contiguous() and out.is_contiguous() and dqkv.is_contiguous()
+    _lib.check(L.bz_flash_attn_bwd(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), dout.data_ptr(), dqkv.data_ptr(),
+                                   _ws[key].data_ptr(), B, S, Hq, Hk, hd, hd ** -0.5, _lib.stream()), "flash_attn_bwd")
+    _lib.add_launches(2)
+    return dqkv
+
+
 def has_bwd() -> bool:
     L = _lib.load()
     return L is not None and hasattr(L, "bz_flash_attn_bwd")

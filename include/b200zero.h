@@ -175,6 +175,16 @@ int bz_ag_gemm_max_tiles(void);
 int bz_ag_gemm_bf16(const void* X, void* const* shard_ptrs, void* Wfull, void* Y, void* chunk_ready, int M, int N,
                     int K, int ldx, int ldc, int rank, int ws, int cta_group, void* stream);
 
+/* ---- K6: flash attention backward ---------------------------------------------------
+ * dqkv (same fused layout as qkv) from qkv, out, lse (from the forward) and dout.
+ * workspace: bz_flash_attn_bwd_workspace_floats(B,S,Hq) floats (fp32 dQ accumulator +
+ * Delta); zeroed by the call. Five tcgen05 GEMMs per (kv block, q tile); dK/dV accumulate
+ * in TMEM; dQ via cp.reduce.async.bulk add.f32. */
+long long bz_flash_attn_bwd_workspace_floats(int B, int S, int Hq);
+int bz_flash_attn_bwd(const void* qkv, const void* out, const float* lse, const void* dout, void* dqkv,
+                      float* workspace, int B, int S, int Hq, int Hk, int head_dim, float softmax_scale,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

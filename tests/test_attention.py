@@ -55,3 +55,24 @@ def test_flash_fwd_large_magnitude_rescale_path():
     out, _ = flash_fwd(qkv, B, S, Hq, Hk, hd)
     ref = A.attention_ref(qkv, B, S, Hq, Hk, hd)
     assert (out.float() - ref).abs().max().item() < 6e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,S,Hq,Hk", [(1, 128, 1, 1), (1, 256, 2, 1), (2, 512, 8, 2), (1, 1024, 4, 4)])
+def test_flash_bwd_matches_autograd_oracle(B, S, Hq, Hk):
+    from distributed_llm_training_gpu_manager_b200.ops.flash import flash_bwd, flash_fwd
+    torch.manual_seed(3)
+    hd = 128
+    qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
+    dout = torch.randn(B * S, Hq * hd, device="cuda").bfloat16()
+    out, lse = flash_fwd(qkv, B, S, Hq, Hk, hd)
+    dqkv = flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd)
+    torch.cuda.synchronize()
+    x = qkv.float().requires_grad_()
+    (A.attention_ref(x, B, S, Hq, Hk, hd) * dout.float()).sum().backward()
+    ref = x.grad
+    for name, lo, hi in (("dq", 0, Hq * hd), ("dk", Hq * hd, (Hq + Hk) * hd), ("dv", (Hq + Hk) * hd, (Hq + 2 * Hk) * hd)):
+        a, b_ = dqkv[:, lo:hi].float(), ref[:, lo:hi]
+        scale = b_.abs().max().item() + 1e-6
+        assert (a - b_).abs().max().item() / scale < 4e-2, (name, (a - b_).abs().max().item(), scale)
+        assert (a - b_).abs().mean().item() / (b_.abs().mean().item() + 1e-9) < 2e-2, name
