@@ -1,0 +1,92 @@
+"""ZeRO-Offload optimizer step (H1 / X9): fp32 master weights and Adam moments live
+in pinned host memory (``offload_optimizer.device = "cpu"``, the reference's default —
+ref ``ai_engine/deepspeed_launcher.py:39,197-203``); each step streams the gradient shard to the
+host in chunks on a side stream, runs the C++ AdamW (``csrc/host/host_adam.cpp``) chunk by chunk,
+and streams the new bf16 weights back, with device→host, host compute and host→device of
+consecutive chunks overlapped (double-buffered pinned staging, ``buffer_count`` ≥ 2)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from ..ops import lib as _lib
+
+_CHUNK = 1 << 26  # 64 Mi elements per chunk (128 MB bf16 down, 128 MB bf16 up)
+
+
+def _host_lib():
+    L = _lib.load_host(required=True)
+    if not getattr(L, "_bz_bound", False):
+        L.bz_host_adamw.restype = C.c_int
+        L.bz_host_adamw.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_longlong,
+                                    C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float, C.c_int]
+        L._bz_bound = True
+    return L
+
+
+def host_adamw(master: torch.Tensor, m: torch.Tensor, v: torch.Tensor, grad: torch.Tensor, out_bf16: Optional[torch.Tensor],
+               *, lr: float, beta1: float, beta2: float, eps: float, weight_decay: float, step: int,
+               grad_scale: float = 1.0, threads: int = 0) -> None:
+    """CPU tensors only. ``grad``: fp32 or bf16; ``out_bf16``: bf16 tensor or None."""
+    L = _host_lib()
+    assert not master.is_cuda and master.dtype == torch.float32
+    rc = L.bz_host_adamw(master.data_ptr(), m.data_ptr(), v.data_ptr(), grad.data_ptr(),
+                         int(grad.dtype == torch.bfloat16), out_bf16.data_ptr() if out_bf16 is not None else None,
+                         master.numel(), lr, beta1, beta2, eps, weight_decay, step, grad_scale, threads)
+    if rc != 0:
+        raise RuntimeError(f"bz_host_adamw failed rc={rc}")
+
+
+def host_adam_step(engine, lr: float, step_no: int) -> None:
+    """Called by ``ZeroEngine._optimizer_step`` when optimizer state is offloaded."""
+    cfg = engine.cfg
+    dev = engine.device
+    n = engine.layout.shard_numel
+    # clip coefficient and skip flag were produced on the device; the host update needs them now
+    host_vals = torch.stack([engine._coef[0], engine._flag[0].float()]).cpu()
+    coef, skip = float(host_vals[0]), bool(host_vals[1] > 0)
+    if skip:
+        return
+    if not hasattr(engine, "_off_stream"):
+        engine._off_stream = torch.cuda.Stream(device=dev)
+        nbuf = 2
+        gdt = engine.shard_grads.dtype
+        engine._off_g = [torch.empty(min(_CHUNK, n), dtype=gdt).pin_memory() for _ in range(nbuf)]
+        engine._off_p = [torch.empty(min(_CHUNK, n), dtype=torch.bfloat16).pin_memory() for _ in range(nbuf)]
+    side = engine._off_stream
+    side.wait_stream(torch.cuda.current_stream())
+    chunks = [(o, min(o + _CHUNK, n)) for o in range(0, n, _CHUNK)]
+    d2h_evt = [None] * len(chunks)
+    h2d_evt = [None] * 2
+
+    def issue_d2h(i):
+        lo, hi = chunks[i]
+        b = i % 2
+        with torch.cuda.stream(side):
+            if h2d_evt[b] is not None:
+                side.wait_event(h2d_evt[b])
+            engine._off_g[b][: hi - lo].copy_(engine.shard_grads[lo:hi], non_blocking=True)
+            d2h_evt[i] = torch.cuda.Event()
+            d2h_evt[i].record(side)
+
+    issue_d2h(0)
+    to_bf16 = engine.compute_dtype == torch.bfloat16
+    for i, (lo, hi) in enumerate(chunks):
+        if i + 1 < len(chunks):
+            issue_d2h(i + 1)
+        d2h_evt[i].synchronize()
+        b = i % 2
+        outp = engine._off_p[b][: hi - lo] if to_bf16 else None
+        host_adamw(engine.master[lo:hi], engine.exp_avg[lo:hi], engine.exp_avg_sq[lo:hi], engine._off_g[b][: hi - lo],
+                   outp, lr=lr, beta1=cfg.betas[0], beta2=cfg.betas[1], eps=cfg.eps, weight_decay=cfg.weight_decay,
+                   step=step_no, grad_scale=coef)
+        with torch.cuda.stream(side):
+            if to_bf16:
+                engine.shard_params[lo:hi].copy_(outp, non_blocking=True)
+            else:
+                engine.shard_params[lo:hi].copy_(engine.master[lo:hi].to(engine.compute_dtype), non_blocking=True)
+            h2d_evt[b] = torch.cuda.Event()
+            h2d_evt[b].record(side)
+    torch.cuda.current_stream().wait_stream(side)

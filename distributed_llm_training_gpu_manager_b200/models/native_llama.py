@@ -97,6 +97,11 @@ class NativeLlamaEngine(ZeroEngine):
         assert self.compute_dtype == torch.bfloat16 or not self.on_cuda, "native kernels are bf16"
         self._saved: Optional[Dict[str, Any]] = None
         self._micro_in_window = 0
+        # K2: with the fused backend at ZeRO-3 every forward GEMM gathers its own weight in-kernel
+        import os
+        self._ag_fused = (self.fused is not None and self.stage >= 3 and self.pooled_params
+                          and os.environ.get("B200ZERO_AG_GEMM", "1") == "1")
+        self._ag_ptrs: Dict[str, Any] = {}
 
     # -------------------------------------------------------------- helpers
     def _w(self, layer: int, name: str) -> torch.Tensor:
@@ -105,19 +110,65 @@ class NativeLlamaEngine(ZeroEngine):
     def _gw(self, layer: int, name: str) -> torch.Tensor:
         return self.grad_view(f"blocks.{layer}.{name}.weight")
 
+    def _unit_is_resident(self, ui: int) -> bool:
+        return self._resident[ui] and (ui == 0 or self._slot_owner[(ui - 1) % 2] == ui)
+
+    def _linear(self, l: int, name: str, x: torch.Tensor, ag: bool) -> torch.Tensor:
+        """y = x · Wᵀ; when ``ag`` the weight is all-gathered inside the GEMM kernel (K2) and left in
+        the block's gathered buffer for the rest of forward / recompute / backward."""
+        w = self._w(l, name)
+        if not ag:
+            return G.linear_fwd(x, w)
+        from ..ops.ag_gemm import ag_linear_fwd
+        full = f"blocks.{l}.{name}.weight"
+        ptrs = self._ag_ptrs.get(full)
+        if ptrs is None:
+            spec = self.layout.by_name[full]
+            assert spec.partitioned, f"{full} is not partitioned; cannot fuse its gather"
+            ptrs = self.fused._ptrs_for(self.shard_params[spec.shard_offset:spec.shard_offset + spec.shard_numel])
+            self._ag_ptrs[full] = ptrs
+        return ag_linear_fwd(x, ptrs, w, self.rank, self.world_size)
+
+    def _begin_block(self, l: int) -> bool:
+        """Make block ``l``'s parameters available. Returns True when the GEMMs must gather their own
+        weights (fused all-gather→GEMM); otherwise the unit is (made) resident by a bulk gather."""
+        ui = l + 1
+        if not self.pooled_params or self._unit_is_resident(ui):
+            evt = self._prefetch_evt.pop(ui, None)
+            if evt is not None:
+                torch.cuda.current_stream().wait_event(evt)
+            return False
+        if not self._ag_fused:
+            self._ensure_resident(ui)
+            return False
+        u = self.layout.units[ui]
+        pb = self._unit_pbuf[ui]
+        for spec in u.params:                      # replicated (persistent) tensors: local copies
+            if not spec.partitioned:
+                pb[spec.full_offset:spec.full_offset + spec.numel].copy_(
+                    self.shard_params[spec.shard_offset:spec.shard_offset + spec.shard_numel])
+        slot = (ui - 1) % 2
+        prev = self._slot_owner[slot]
+        if prev is not None and prev != ui:
+            self._resident[prev] = False
+        self._slot_owner[slot] = ui
+        self._resident[ui] = True                  # true once the four AG-GEMMs below have run (stream order)
+        return True
+
     def _block_fwd(self, l: int, x: torch.Tensor, keep: bool) -> Tuple[torch.Tensor, Optional[Dict[str, Any]]]:
         c = self.mcfg
         B, S = self._B, self.seq_len
         Hq, Hk, hd, F_ = c.n_heads, c.n_kv_heads, c.head_dim, c.ffn
+        ag = self._begin_block(l)
         h1, rstd1, _ = E.rmsnorm_fwd(x, self._w(l, "attn_norm"), c.norm_eps)
-        qkv = G.linear_fwd(h1, self._w(l, "wqkv"))
+        qkv = self._linear(l, "wqkv", h1, ag)
         E.rope_(qkv, S, Hq + Hk, hd, c.rope_theta)
         attn, actx = A.attention_fwd(qkv, B, S, Hq, Hk, hd, backend=self.attn_backend)
-        o = G.linear_fwd(attn, self._w(l, "wo"))
+        o = self._linear(l, "wo", attn, ag)
         h2, rstd2, x1 = E.rmsnorm_fwd(x, self._w(l, "ffn_norm"), c.norm_eps, delta=o)
-        gu = G.linear_fwd(h2, self._w(l, "w_gate_up"))
+        gu = self._linear(l, "w_gate_up", h2, ag)
         act = E.swiglu_fwd(gu)
-        dn = G.linear_fwd(act, self._w(l, "w_down"))
+        dn = self._linear(l, "w_down", act, ag)
         x2 = E.add(x1, dn, out=dn)
         if not keep:
             return x2, None
@@ -167,10 +218,8 @@ class NativeLlamaEngine(ZeroEngine):
             x = E.embedding_fwd(ids_flat, self.param_view("embed.weight"))
             ckpts: List[torch.Tensor] = []
             for l in range(L):
-                if self.pooled_params:
-                    self._ensure_resident(l + 1)
-                    if l + 2 <= L:
-                        self._prefetch(l + 2)
+                if self.pooled_params and not self._ag_fused and l + 2 <= L:
+                    self._prefetch(l + 2)          # bulk gather of the next block on the side stream
                 ckpts.append(x)
                 x, _ = self._block_fwd(l, x, keep=False)
             hf, rstd_f, _ = E.rmsnorm_fwd(x, self.param_view("final_norm.weight"), c.norm_eps)
@@ -218,10 +267,8 @@ class NativeLlamaEngine(ZeroEngine):
                                   rstd=sv["rstd_f"], dw_out=self.grad_view("final_norm.weight"), dw_accumulate=acc)
             for l in range(L - 1, -1, -1):
                 ui = l + 1
-                if self.pooled_params:
-                    self._ensure_resident(ui)
-                    if ui - 1 >= 1:
-                        self._prefetch(ui - 1)
+                if self.pooled_params and not self._ag_fused and ui - 1 >= 1:
+                    self._prefetch(ui - 1)
                 if self.pooled_grads and self.on_cuda:
                     evt = self._gslot_free_evt[(ui - 1) % 2]
                     if evt is not None:

@@ -26,7 +26,7 @@ def native_available() -> bool:
     if not _lib.available():
         return False
     L = _lib.load()
-    return hasattr(L, "bz_flash_attn_fwd")
+    return hasattr(L, "bz_flash_attn_fwd") and hasattr(L, "bz_flash_attn_bwd")
 
 
 def _split(qkv: torch.Tensor, B: int, S: int, Hq: int, Hk: int, hd: int):

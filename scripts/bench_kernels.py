@@ -32,6 +32,16 @@ def sdpa():
     return torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=True, enable_gqa=True)
 ms = timeit(sdpa)
 res["sdpa_fwd"] = {"ms": ms, "tflops": fl / ms / 1e9}
+from distributed_llm_training_gpu_manager_b200.ops.flash import flash_bwd
+out, lse = flash_fwd(qkv, B, S, Hq, Hk, hd)
+dout = torch.randn_like(out)
+ms = timeit(lambda: flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd))
+res["flash_bwd"] = {"ms": ms, "tflops": 2.5 * fl / ms / 1e9}
+q_, k_, v_ = (t.detach().requires_grad_() for t in A._split(qkv, B, S, Hq, Hk, hd))
+o_ = torch.nn.functional.scaled_dot_product_attention(q_, k_, v_, is_causal=True, enable_gqa=True)
+do_ = dout.view(B, S, Hq, hd).transpose(1, 2)
+ms = timeit(lambda: torch.autograd.grad(o_, (q_, k_, v_), do_, retain_graph=True))
+res["sdpa_bwd"] = {"ms": ms, "tflops": 2.5 * fl / ms / 1e9}
 print(res, flush=True)
 ws, M = 8, 8192
 for name, N, K in [("qkv", 6144, 4096), ("gate_up", 28672, 4096), ("down", 4096, 14336), ("o", 4096, 4096)]:
