@@ -82,17 +82,23 @@ class Trainer:
         self._preempted = True
 
     # ------------------------------------------------------------------
-    def _maybe_resume(self) -> None:
+    def _maybe_resume(self) -> bool:
         c = self.cfg
         if not (c.resume and c.save_dir):
-            return
-        tag = ckpt.find_rollback_tag(c.save_dir, None, deep=True)
+            return False
+        # every rank must take the same branch: rank 0 looks at the filesystem, the rest follow
+        tag = ckpt.find_rollback_tag(c.save_dir, None, deep=True) if self.engine.rank == 0 else None
+        if dist.is_available() and dist.is_initialized() and self.engine.world_size > 1:
+            box = [tag]
+            dist.broadcast_object_list(box, src=0)
+            tag = box[0]
         if tag is None:
-            return
+            return False
         _, client = self.engine.load_checkpoint(c.save_dir, tag)
         if client.get("monitor"):
             self.monitor.load_state_dict(client["monitor"])
         self._log(f"resumed from {tag} at step {self.engine.global_steps}")
+        return True
 
     def _save(self, tag: Optional[str] = None, sync: bool = False) -> None:
         c = self.cfg
@@ -114,7 +120,11 @@ class Trainer:
         ckpt.wait_for_pending_writes()
         if dist.is_available() and dist.is_initialized() and self.engine.world_size > 1:
             dist.barrier()
-        tag = ckpt.find_rollback_tag(c.save_dir, before_step=bad_step, deep=True)
+        tag = ckpt.find_rollback_tag(c.save_dir, before_step=bad_step, deep=True) if self.engine.rank == 0 else None
+        if dist.is_available() and dist.is_initialized() and self.engine.world_size > 1:
+            box = [tag]
+            dist.broadcast_object_list(box, src=0)
+            tag = box[0]
         if tag is None:
             return False
         self.engine.load_checkpoint(c.save_dir, tag)
@@ -127,8 +137,8 @@ class Trainer:
     # ------------------------------------------------------------------
     def run(self) -> TrainResult:
         eng, c = self.engine, self.cfg
-        self._maybe_resume()
-        if c.save_dir and c.save_every and eng.global_steps == 0 and not ckpt.list_tags(c.save_dir):
+        resumed = self._maybe_resume()
+        if c.save_dir and c.save_every and not resumed and eng.global_steps == 0:
             self._save(sync=True)  # step-0 anchor: a rollback target always exists
         status = "finished"
         steps_run = 0

@@ -172,3 +172,34 @@ def test_launcher_spike_halt_rollback_resume(tmp_path):
     assert out["steps_run"] == 40 + 6            # steps 21..26 were replayed
     assert out["halt_latency_ms"] and out["halt_latency_ms"][0] < 50
     assert out["losses"][-1] < out["losses"][0]
+
+
+def test_supervisor_restarts_after_rank_kill_and_resumes(tmp_path):
+    """BASELINE.json config 4 (CPU tier): a rank is SIGKILLed mid-run (spot preemption of one
+    worker); the supervisor tears the job down, relaunches it, and the workers resume from the
+    newest verified checkpoint and finish."""
+    cfg = DeepSpeedConfig(model_name="tiny", zero_stage=ZeROStage.GRADIENT_PARTITIONING,
+                          offload_optimizer=OffloadDevice.NONE, offload_param=OffloadDevice.NONE, fp16_enabled=False,
+                          train_micro_batch_size_per_gpu=4, gradient_accumulation_steps=1, learning_rate=3e-3,
+                          warmup_steps=5, total_training_steps=200, num_gpus=2, master_port=free_port(),
+                          wall_clock_breakdown=False)
+    launcher = DeepSpeedLauncher()
+    result_file = tmp_path / "result.json"
+    env_backup = dict(os.environ)
+    os.environ.update(B200ZERO_KILL_RANK_AT="17:1", B200ZERO_BACKEND="gloo", MASTER_ADDR="127.0.0.1",
+                      B200ZERO_MAX_RESTARTS="2", B200ZERO_INJECT_NAN_GRAD_AT="23")
+    try:
+        res = launcher.launch(cfg, "builtin:gpt2-tiny",
+                              ["--steps=30", f"--save_dir={tmp_path / 'ckpt'}", "--save_every=5",
+                               f"--result={result_file}", "--seq_len=32", "--window=20"])
+        rec = launcher.registry.wait(res.job_id, timeout=600)
+    finally:
+        os.environ.clear(); os.environ.update(env_backup)
+    log = launcher.registry.tail(res.job_id) or ""
+    assert rec is not None and rec.returncode == 0, log
+    assert "restart 1/2" in log and "resumed from global_step15" in log, log
+    out = json.loads(result_file.read_text())
+    assert out["status"] == "finished" and out["final_step"] == 30
+    # the NaN gradient injected at step 23 (after the restart) was caught, the update skipped, and
+    # the run rolled back to the last good checkpoint and carried on
+    assert "divergence" in out["alerts"] and out["rollbacks"] == 1, out
