@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--comm", default="auto", help="auto | nccl | fused")
     ap.add_argument("--attn", default=None, help="attention backend override: native | sdpa")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model (result is not a bench value)")
     return ap.parse_args()
 
 
@@ -155,7 +156,7 @@ def run_ours(args) -> int:
     from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
     from distributed_llm_training_gpu_manager_b200.ops import lib as bzlib
 
-    mcfg = get_config(args.model)
+    mcfg = get_config(args.model, **({"n_layers": args.layers} if args.layers else {}))
     S, MB = args.seq_len, args.micro_batch
     # The launcher's own auto-config drives the engine (public API path): ZeRO-3, bf16, no offload
     # (8B fits in 180 GB HBM3e per GPU even unsharded), clipping 1.0, WarmupDecayLR.
@@ -237,7 +238,8 @@ def run_ours(args) -> int:
         "warmup": args.warmup, "ms_per_step": round(ms_total / args.steps, 2), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic tokens, random-init weights",
-        "config": {"model": args.model, "global_batch": MB * world, "seq_len": S,
+        "config": {"model": args.model + (f"[TRUNCATED to {args.layers} layers: profiling only]" if args.layers else ""),
+                   "global_batch": MB * world, "seq_len": S,
                    "parallelism": f"zero3-dp{world}", "micro_batch_per_gpu": MB, "optimizer": "AdamW fp32 master",
                    "grad_clip": 1.0, "activation_recompute": True, "comm": engine.comm_mode,
                    "attention": args.attn or "auto",
