@@ -226,7 +226,7 @@ def run_ours(args) -> int:
     ms_total, e2e_total = float(t[0]), float(t[1])
     tokens_per_step = MB * S * world
     value = tokens_per_step * args.steps / (ms_total / 1e3)
-    flops_tok = mcfg.flops_per_token(S, recompute=True)
+    flops_tok = mcfg.flops_per_token(S, recompute=False)      # model FLOPs (6·N + attention): recompute not counted
     peaks = {}
     try:
         peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
@@ -241,7 +241,7 @@ def run_ours(args) -> int:
         "config": {"model": args.model + (f"[TRUNCATED to {args.layers} layers: profiling only]" if args.layers else ""),
                    "global_batch": MB * world, "seq_len": S,
                    "parallelism": f"zero3-dp{world}", "micro_batch_per_gpu": MB, "optimizer": "AdamW fp32 master",
-                   "grad_clip": 1.0, "activation_recompute": True, "comm": engine.comm_mode,
+                   "grad_clip": 1.0, "activation_recompute": engine.recompute, "comm": engine.comm_mode,
                    "attention": args.attn or "auto",
                    "l2": "working set (16 GB weights + 96 GB optimizer state) >> 126 MB L2; no flush needed"},
         "clocks": clocks, "gpu_launches": launches, "impl": args.impl,

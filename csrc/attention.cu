@@ -22,10 +22,10 @@ namespace bz {
 constexpr int FA_HD = 128;
 constexpr int FA_BM = 128;  // query rows per CTA
 constexpr int FA_BN = 128;  // kv rows per block
-constexpr int FA_THREADS = 192;
+constexpr int FA_THREADS = 320;  // TMA warp, MMA warp, 8 softmax warps (two threads per query row)
 constexpr int FA_TILE_BYTES = 128 * 128 * 2;  // 32 KB: two 64-column halves of 16 KB
 constexpr int FA_HALF_BYTES = 128 * 64 * 2;
-constexpr int FA_SMEM = 6 * FA_TILE_BYTES /*Q,K0,K1,V0,V1,P*/ + 256 + 1024;
+constexpr int FA_SMEM = 6 * FA_TILE_BYTES /*Q,K0,K1,V0,V1,P*/ + 256 + 3 * 2 * 128 * 4 /*pair exchange*/ + 1024;
 constexpr float FA_RESCALE_THRESHOLD = 8.f;
 
 struct FaBars {
@@ -68,9 +68,9 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restri
       mbar_init(bar + FaBars::v_full + 8 * i, 1);
       mbar_init(bar + FaBars::v_empty + 8 * i, 1);
       mbar_init(bar + FaBars::s_full + 8 * i, 1);
-      mbar_init(bar + FaBars::s_empty + 8 * i, 128);
+      mbar_init(bar + FaBars::s_empty + 8 * i, 256);
     }
-    mbar_init(bar + FaBars::p_full, 128);
+    mbar_init(bar + FaBars::p_full, 256);
     mbar_init(bar + FaBars::pv_done, 1);
     fence_barrier_init();
   } else if (warp == 1) {
@@ -144,93 +144,88 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restri
       }
     }
   } else {
-    // ------------------------------ softmax: one thread per query row ------------------------------
-    const int q = warp & 3;
-    const int r = q * 32 + lane;            // row inside the tile == TMEM lane
+    // ---------------- softmax: two threads per query row, each owning 64 of the 128 kv columns ----------------
+    const int q = warp & 3;                       // TMEM lane quadrant of this warp
+    const int hf = (warp - 2) >> 2;               // which half of the columns (warps 2-5: 0, warps 6-9: 1)
+    const int r = q * 32 + lane;                  // query row inside the tile == TMEM lane
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    float m_used = -INFINITY;               // exponent reference currently baked into O and l (log2 domain)
-    float l = 0.f;
+    float* xch = reinterpret_cast<float*>(smem_raw + (bar + 256 - smem_u32(smem_raw)));  // [3][2][128]
+    float m_used = -INFINITY;                     // exponent reference baked into O and l (log2 domain)
+    float l = 0.f;                                // this thread's share of the row sum
     for (int j = 0; j < nblk; ++j) {
       const int st = j & 1;
       const uint32_t ph = (j >> 1) & 1;
       const bool diag = (j == nblk - 1);
       mbar_wait(bar + FaBars::s_full + 8 * st, ph);
       tc_fence_after();
-      // pass 1: row max
+      uint32_t sv[64];
+      tmem_ld_32x64(tm_s[st] + lane_off + hf * 64, sv);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(bar + FaBars::s_empty + 8 * st);          // S[st] is in registers: block j+2 may overwrite it
       float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(tm_s[st] + lane_off + c * 32, v);
-        tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const float s = __uint_as_float(v[e]);
-          if (!diag || (c * 32 + e) <= r) mx = fmaxf(mx, s);
-        }
+      for (int e = 0; e < 64; ++e) {
+        float s = __uint_as_float(sv[e]) * scale_log2;
+        if (diag && (hf * 64 + e) > r) s = -INFINITY;
+        sv[e] = __float_as_uint(s);
+        mx = fmaxf(mx, s);
       }
-      const float m_new = fmaxf(m_used, mx * scale_log2);
-      // lazy rescale: only when the reference exponent is too stale (or on the very first block)
-      const bool need = (m_new - m_used) > FA_RESCALE_THRESHOLD;   // true when m_used == -inf
-      if (j > 0) mbar_wait(bar + FaBars::pv_done, (j - 1) & 1);    // O and the P buffer are free again
+      // combine the two halves of the row
+      float* xm = xch + (j & 1) * 256;
+      xm[hf * 128 + r] = mx;
+      asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
+      mx = fmaxf(mx, xm[(hf ^ 1) * 128 + r]);
+      const float m_new = fmaxf(m_used, mx);
+      const bool need = (m_new - m_used) > FA_RESCALE_THRESHOLD;     // lazy rescale (always true on block 0)
+      if (j > 0) mbar_wait(bar + FaBars::pv_done, (j - 1) & 1);     // O and the P buffer are free again
       if (__any_sync(0xffffffffu, need) && j > 0) {
         tc_fence_after();
-        const float alpha = need ? exp2f(m_used - m_new) : 1.f;
+        const float alpha = need ? fast_exp2(m_used - m_new) : 1.f;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           uint32_t v[32];
-          tmem_ld_32x32(tm_o + lane_off + c * 32, v);
+          tmem_ld_32x32(tm_o + lane_off + hf * 64 + c * 32, v);
           tmem_ld_wait();
 #pragma unroll
           for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) * alpha);
-          tmem_st_32x32(tm_o + lane_off + c * 32, v);
+          tmem_st_32x32(tm_o + lane_off + hf * 64 + c * 32, v);
         }
         tmem_st_wait();
+        tc_fence_before();
         l *= alpha;
       }
       if (need) m_used = m_new;
-      // pass 2: P = exp2(s*scale - m_used) -> bf16 -> swizzled smem (K-major, 2 halves of 64 kv columns)
       float rs = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(tm_s[st] + lane_off + c * 32, v);
-        tmem_ld_wait();
-        uint32_t pk[16];
+      uint32_t pk[32];
 #pragma unroll
-        for (int e = 0; e < 32; e += 2) {
-          float p0 = exp2f(__uint_as_float(v[e]) * scale_log2 - m_used);
-          float p1 = exp2f(__uint_as_float(v[e + 1]) * scale_log2 - m_used);
-          if (diag) {
-            if (c * 32 + e > r) p0 = 0.f;
-            if (c * 32 + e + 1 > r) p1 = 0.f;
-          }
-          rs += p0 + p1;
-          pk[e >> 1] = pack_bf16x2(p0, p1);
-        }
-        // columns [c*32, c*32+32) -> half (c>>1), 16-byte chunks ((c&1)*4 + i), XOR-swizzled by row
-        const uint32_t rowb = p_s + (c >> 1) * FA_HALF_BYTES + r * 128;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int chunk = ((c & 1) * 4 + i) ^ (r & 7);
-          st_shared_v4(rowb + chunk * 16, pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
-        }
+      for (int e = 0; e < 64; e += 2) {
+        const float p0 = fast_exp2(__uint_as_float(sv[e]) - m_used);
+        const float p1 = fast_exp2(__uint_as_float(sv[e + 1]) - m_used);
+        rs += p0 + p1;
+        pk[e >> 1] = pack_bf16x2(p0, p1);
       }
       l += rs;
-      tc_fence_before();
-      mbar_arrive(bar + FaBars::s_empty + 8 * st);   // S[st] may be overwritten by block j+2
+      const uint32_t rowb = p_s + hf * FA_HALF_BYTES + r * 128;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        st_shared_v4(rowb + ((i ^ (r & 7)) * 16), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
       fence_proxy_async_smem();                      // make P visible to the tensor core (async proxy)
       mbar_arrive(bar + FaBars::p_full);
     }
-    // epilogue: O / l -> bf16, LSE
+    // epilogue: combine l, O / l -> bf16, LSE
+    float* xl = xch + 2 * 256;
+    xl[hf * 128 + r] = l;
+    asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
+    l += xl[(hf ^ 1) * 128 + r];
     mbar_wait(bar + FaBars::pv_done, (nblk - 1) & 1);
     tc_fence_after();
     const float inv_l = 1.f / l;
-    __nv_bfloat16* orow = out + (size_t)(row0 + r) * ld_out + h * FA_HD;
+    __nv_bfloat16* orow = out + (size_t)(row0 + r) * ld_out + h * FA_HD + hf * 64;
 #pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < 2; ++c) {
       uint32_t v[32];
-      tmem_ld_32x32(tm_o + lane_off + c * 32, v);
+      tmem_ld_32x32(tm_o + lane_off + hf * 64 + c * 32, v);
       tmem_ld_wait();
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -242,7 +237,8 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restri
         *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = o;
       }
     }
-    if (lse != nullptr) lse[(size_t)h * ((size_t)B * S) + row0 + r] = (m_used + log2f(l)) * 0.6931471805599453f;
+    if (lse != nullptr && hf == 0)
+      lse[(size_t)h * ((size_t)B * S) + row0 + r] = (m_used + log2f(l)) * 0.6931471805599453f;
   }
 
   tc_fence_before();

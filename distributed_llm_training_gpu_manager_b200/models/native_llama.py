@@ -83,7 +83,7 @@ class NativeLlamaEngine(ZeroEngine):
 
     def __init__(self, model_cfg: ModelConfig, config: Union[str, Dict[str, Any], EngineConfig], *, seq_len: int,
                  device: Optional[torch.device] = None, comm: str = "auto", seed: int = 1234,
-                 attn_backend: Optional[str] = None, head_chunk: int = 2048):
+                 attn_backend: Optional[str] = None, head_chunk: int = 2048, recompute: Optional[str] = None):
         assert model_cfg.family == "llama"
         ecfg = load_config(config)
         if device is None:
@@ -97,6 +97,15 @@ class NativeLlamaEngine(ZeroEngine):
         assert self.compute_dtype == torch.bfloat16 or not self.on_cuda, "native kernels are bf16"
         self._saved: Optional[Dict[str, Any]] = None
         self._micro_in_window = 0
+        # Activation policy (``activation_checkpointing`` block of the config):
+        #   full      — keep only each block's input, recompute the whole block in backward
+        #   selective — keep everything except the two largest tensors (gate|up and silu·up, 0.7 GB per
+        #               block at 8k tokens) and recompute just that GEMM + SwiGLU; default when the
+        #               config enables activation checkpointing (180 GB HBM3e leaves room for the rest)
+        #   none      — keep everything (config has no activation_checkpointing block)
+        import os as _os
+        self.recompute = recompute or _os.environ.get("B200ZERO_RECOMPUTE") or ("selective" if self.cfg.act_ckpt else "none")
+        assert self.recompute in ("full", "selective", "none")
         # K2: with the fused backend at ZeRO-3 every forward GEMM gathers its own weight in-kernel
         import os
         self._ag_fused = (self.fused is not None and self.stage >= 3 and self.pooled_params
@@ -155,6 +164,12 @@ class NativeLlamaEngine(ZeroEngine):
         self._resident[ui] = True                  # true once the four AG-GEMMs below have run (stream order)
         return True
 
+    def _begin_block_bwd(self, l: int) -> None:
+        """Backward needs every weight of the block resident (bulk gather, prefetched one block ahead)."""
+        ui = l + 1
+        if self.pooled_params:
+            self._ensure_resident(ui)
+
     def _block_fwd(self, l: int, x: torch.Tensor, keep: bool) -> Tuple[torch.Tensor, Optional[Dict[str, Any]]]:
         c = self.mcfg
         B, S = self._B, self.seq_len
@@ -174,11 +189,18 @@ class NativeLlamaEngine(ZeroEngine):
             return x2, None
         return x2, dict(h1=h1, rstd1=rstd1, attn=attn, actx=actx, x1=x1, rstd2=rstd2, h2=h2, gu=gu, act=act)
 
-    def _block_bwd(self, l: int, x: torch.Tensor, dx2: torch.Tensor, acc: bool) -> torch.Tensor:
+    def _block_bwd(self, l: int, x: torch.Tensor, dx2: torch.Tensor, acc: bool,
+                   sv: Optional[Dict[str, Any]] = None) -> torch.Tensor:
         c = self.mcfg
         S = self.seq_len
         Hq, Hk, hd = c.n_heads, c.n_kv_heads, c.head_dim
-        _, sv = self._block_fwd(l, x, keep=True)                      # recompute
+        if sv is None:
+            _, sv = self._block_fwd(l, x, keep=True)                  # full recompute
+        else:
+            self._begin_block_bwd(l)
+            if "gu" not in sv:                                        # selective: redo gate|up GEMM + SwiGLU only
+                sv["gu"] = G.linear_fwd(sv["h2"], self._w(l, "w_gate_up"))
+                sv["act"] = E.swiglu_fwd(sv["gu"])
         adt = dict(accumulate=acc)
         # MLP
         G.linear_wgrad(dx2, sv["act"], out=self._gw(l, "w_down"), **adt)
@@ -217,11 +239,15 @@ class NativeLlamaEngine(ZeroEngine):
             ids_flat, labels_flat = ids.reshape(-1), labels.reshape(-1)
             x = E.embedding_fwd(ids_flat, self.param_view("embed.weight"))
             ckpts: List[torch.Tensor] = []
+            saved_acts: List[Optional[Dict[str, Any]]] = []
             for l in range(L):
                 if self.pooled_params and not self._ag_fused and l + 2 <= L:
                     self._prefetch(l + 2)          # bulk gather of the next block on the side stream
                 ckpts.append(x)
-                x, _ = self._block_fwd(l, x, keep=False)
+                x, sv_l = self._block_fwd(l, x, keep=self.recompute != "full")
+                if sv_l is not None and self.recompute == "selective":
+                    sv_l.pop("gu"); sv_l.pop("act")
+                saved_acts.append(sv_l)
             hf, rstd_f, _ = E.rmsnorm_fwd(x, self.param_view("final_norm.weight"), c.norm_eps)
             # LM head + CE, chunked over tokens; gradients of the head are produced here
             w_head, g_head = self.param_view("lm_head.weight"), self.grad_view("lm_head.weight")
@@ -241,7 +267,7 @@ class NativeLlamaEngine(ZeroEngine):
                 G.linear_wgrad(logits, hf[t0:t1], out=g_head, accumulate=(acc or ci > 0))
                 del logits
             loss = loss_tok.sum() * inv_valid
-        self._saved = dict(ids=ids_flat, ckpts=ckpts, x_last=x, rstd_f=rstd_f, dhf=dhf, acc=acc)
+        self._saved = dict(ids=ids_flat, ckpts=ckpts, acts=saved_acts, x_last=x, rstd_f=rstd_f, dhf=dhf, acc=acc)
         return loss
 
     _all_valid = True
@@ -267,14 +293,15 @@ class NativeLlamaEngine(ZeroEngine):
                                   rstd=sv["rstd_f"], dw_out=self.grad_view("final_norm.weight"), dw_accumulate=acc)
             for l in range(L - 1, -1, -1):
                 ui = l + 1
-                if self.pooled_params and not self._ag_fused and ui - 1 >= 1:
+                if self.pooled_params and ui - 1 >= 1 and (not self._ag_fused or self.recompute != "full"):
                     self._prefetch(ui - 1)
                 if self.pooled_grads and self.on_cuda:
                     evt = self._gslot_free_evt[(ui - 1) % 2]
                     if evt is not None:
                         torch.cuda.current_stream().wait_event(evt)
-                dx = self._block_bwd(l, sv["ckpts"][l], dx, acc)
+                dx = self._block_bwd(l, sv["ckpts"][l], dx, acc, sv["acts"][l])
                 sv["ckpts"][l] = None
+                sv["acts"][l] = None
                 if self._reduce_now:
                     self._reduce_unit(ui)
             E.embedding_bwd(sv["ids"], dx, self.grad_view("embed.weight"))
