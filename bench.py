@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--comm", default="auto", help="auto | nccl | fused")
     ap.add_argument("--attn", default=None, help="attention backend override: native | sdpa")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--breakdown", action="store_true", help="after the timed region, run one extra step with per-phase CUDA-event timers")
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model (result is not a bench value)")
     return ap.parse_args()
 
@@ -194,12 +195,14 @@ def run_ours(args) -> int:
     launches0 = bzlib.launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
+    torch.cuda.profiler.start()      # lets `ncu --profile-from-start off` skip model construction
     e0.record()
     last = None
     for i in range(args.steps):
         last = engine.train_step(*dev[i % n_pool])
     e1.record()
     sync_all()
+    torch.cuda.profiler.stop()
     ms_total = e0.elapsed_time(e1)
     launches = bzlib.launches() - launches0
     clocks = sampler.stop()
@@ -218,6 +221,18 @@ def run_ours(args) -> int:
             _ = float(m["loss"])
         sync_all()
         e2e_ms = (time.perf_counter() - t0) * 1e3
+
+    breakdown = None
+    if args.breakdown:
+        engine.timers.enabled = True
+        engine.cfg.wall_clock_breakdown = True
+        sync_all()
+        t0 = time.perf_counter()
+        m = engine.train_step(*dev[0])
+        sync_all()
+        breakdown = dict(m.get("timers_ms", {}), wall_ms=(time.perf_counter() - t0) * 1e3)
+        engine.timers.enabled = False
+        engine.cfg.wall_clock_breakdown = False
 
     # ---- max over ranks ----
     t = torch.tensor([ms_total, e2e_ms or 0.0], device=device, dtype=torch.float64)
@@ -249,6 +264,8 @@ def run_ours(args) -> int:
         "mfu_vs_measured_cublas_sustained": round(per_gpu_tflops / peaks.get("bf16_tflops_sustained", 1358.3), 3),
         "final_loss": last["loss"] if last else None,
     }
+    if breakdown is not None:
+        out["breakdown_ms"] = {k: round(v, 2) for k, v in breakdown.items()}
     if e2e_ms is not None:
         out["e2e"] = {"value": round(tokens_per_step * args.steps / (e2e_total / 1e3), 1), "unit": "tokens/s",
                       "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -292,7 +292,7 @@ extern "C" int bz_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, 
 namespace bz {
 
 constexpr int FB_QT = 64;                       // query rows per inner tile
-constexpr int FB_THREADS = 192;
+constexpr int FB_THREADS = 320;                // TMA warp, MMA warp, 8 compute warps (two threads per TMEM lane)
 constexpr int FB_KV_BYTES = 128 * 128 * 2;      // 32 KB, two halves of 16 KB
 constexpr int FB_KV_HALF = 128 * 64 * 2;
 constexpr int FB_Q_BYTES = FB_QT * 128 * 2;     // 16 KB, two halves of 8 KB
@@ -350,11 +350,11 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
     }
     mbar_init(bar + FbBars::st_full, 1);
     mbar_init(bar + FbBars::dp_full, 1);
-    mbar_init(bar + FbBars::pt_ready, 128);
-    mbar_init(bar + FbBars::dst_ready, 128);
+    mbar_init(bar + FbBars::pt_ready, 256);
+    mbar_init(bar + FbBars::dst_ready, 256);
     mbar_init(bar + FbBars::dq_full, 1);
-    mbar_init(bar + FbBars::sdp_empty, 128);
-    mbar_init(bar + FbBars::dqt_empty, 128);
+    mbar_init(bar + FbBars::sdp_empty, 256);
+    mbar_init(bar + FbBars::dqt_empty, 256);
     mbar_init(bar + FbBars::acc_full, 1);
     fence_barrier_init();
   } else if (warp == 1) {
@@ -435,8 +435,9 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
     }
   } else {
     const int q4 = warp & 3;
+    const int hf = (warp - 2) >> 2;                          // which 32 of the 64 query columns this thread owns
     const int r = q4 * 32 + lane;                            // kv row (S^T, dP^T, dV, dK) / hd index (dQ^T)
-    const int ct = (warp - 2) * 32 + lane;                   // 0..127 thread index among compute warps
+    const int ct = (warp - 2) * 32 + lane;                   // 0..255 among the compute warps
     const uint32_t lane_off = (uint32_t)(q4 * 32) << 16;
     const int kv_pos = j * 128 + r;
     for (int it = 0; it < iters; ++it) {
@@ -447,52 +448,51 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       // stage lse / delta of this query tile
       float* sl = stat + (it & 1) * 2 * FB_QT;
       if (ct < FB_QT) sl[ct] = lse[(size_t)h * T + (size_t)b * S + q_pos0 + ct] * 1.4426950408889634f;
-      else sl[ct] = delta[(size_t)h * T + (size_t)b * S + q_pos0 + (ct - FB_QT)];
-      asm volatile("bar.sync 2, 128;" ::: "memory");
+      else if (ct < 2 * FB_QT) sl[ct] = delta[(size_t)h * T + (size_t)b * S + q_pos0 + (ct - FB_QT)];
+      asm volatile("bar.sync 2, 256;" ::: "memory");
       const bool diag = q_pos0 < j * 128 + 128;
+      const int c0 = hf * 32;                                // first query column of this thread
       // ---- P^T ----
       mbar_wait(bar + FbBars::st_full, par);
       tc_fence_after();
-      uint32_t pk[32];                                       // P^T row as packed bf16 (64 values)
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      uint32_t pk[16];                                       // 32 probabilities as packed bf16
+      {
         uint32_t v[32];
-        tmem_ld_32x32(tm_st + lane_off + c * 32, v);
+        tmem_ld_32x32(tm_st + lane_off + c0, v);
         tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
-          float p0 = exp2f(__uint_as_float(v[e]) * scale_log2 - sl[c * 32 + e]);
-          float p1 = exp2f(__uint_as_float(v[e + 1]) * scale_log2 - sl[c * 32 + e + 1]);
+          float p0 = fast_exp2(__uint_as_float(v[e]) * scale_log2 - sl[c0 + e]);
+          float p1 = fast_exp2(__uint_as_float(v[e + 1]) * scale_log2 - sl[c0 + e + 1]);
           if (diag) {
-            if (kv_pos > q_pos0 + c * 32 + e) p0 = 0.f;
-            if (kv_pos > q_pos0 + c * 32 + e + 1) p1 = 0.f;
+            if (kv_pos > q_pos0 + c0 + e) p0 = 0.f;
+            if (kv_pos > q_pos0 + c0 + e + 1) p1 = 0.f;
           }
-          pk[c * 16 + (e >> 1)] = pack_bf16x2(p0, p1);
+          pk[e >> 1] = pack_bf16x2(p0, p1);
         }
       }
       {
         const uint32_t rowb = pt_s + r * 128;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          st_shared_v4(rowb + ((i ^ (r & 7)) * 16), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        for (int i = 0; i < 4; ++i)
+          st_shared_v4(rowb + (((hf * 4 + i) ^ (r & 7)) * 16), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
       }
       fence_proxy_async_smem();
       mbar_arrive(bar + FbBars::pt_ready);
       // ---- dS^T = P^T * (dP^T - Delta) * scale ----
       mbar_wait(bar + FbBars::dp_full, par);
       tc_fence_after();
-      uint32_t dk_[32];
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      uint32_t dk_[16];
+      {
         uint32_t v[32];
-        tmem_ld_32x32(tm_dp + lane_off + c * 32, v);
+        tmem_ld_32x32(tm_dp + lane_off + c0, v);
         tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
-          const float2 p = unpack_bf16x2(pk[c * 16 + (e >> 1)]);
-          const float d0 = p.x * (__uint_as_float(v[e]) - sl[FB_QT + c * 32 + e]) * scale;
-          const float d1 = p.y * (__uint_as_float(v[e + 1]) - sl[FB_QT + c * 32 + e + 1]) * scale;
-          dk_[c * 16 + (e >> 1)] = pack_bf16x2(d0, d1);
+          const float2 p = unpack_bf16x2(pk[e >> 1]);
+          const float d0 = p.x * (__uint_as_float(v[e]) - sl[FB_QT + c0 + e]) * scale;
+          const float d1 = p.y * (__uint_as_float(v[e + 1]) - sl[FB_QT + c0 + e + 1]) * scale;
+          dk_[e >> 1] = pack_bf16x2(d0, d1);
         }
       }
       tc_fence_before();
@@ -500,8 +500,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       {
         const uint32_t rowb = dst_s + r * 128;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          st_shared_v4(rowb + ((i ^ (r & 7)) * 16), dk_[4 * i], dk_[4 * i + 1], dk_[4 * i + 2], dk_[4 * i + 3]);
+        for (int i = 0; i < 4; ++i)
+          st_shared_v4(rowb + (((hf * 4 + i) ^ (r & 7)) * 16), dk_[4 * i], dk_[4 * i + 1], dk_[4 * i + 2], dk_[4 * i + 3]);
       }
       fence_proxy_async_smem();
       mbar_arrive(bar + FbBars::dst_ready);
@@ -509,19 +509,18 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       mbar_wait(bar + FbBars::dq_full, par);
       tc_fence_after();
       if (ct == 0) tma_store_wait_read<0>();                 // previous bulk reduce finished reading staging
-      asm volatile("bar.sync 2, 128;" ::: "memory");
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      {
         uint32_t v[32];
-        tmem_ld_32x32(tm_dq + lane_off + c * 32, v);
+        tmem_ld_32x32(tm_dq + lane_off + c0, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 32; ++e) stg[(c * 32 + e) * 128 + r] = __uint_as_float(v[e]);
+        for (int e = 0; e < 32; ++e) stg[(c0 + e) * 128 + r] = __uint_as_float(v[e]);
       }
       tc_fence_before();
       mbar_arrive(bar + FbBars::dqt_empty);
       fence_proxy_async_smem();
-      asm volatile("bar.sync 2, 128;" ::: "memory");
+      asm volatile("bar.sync 2, 256;" ::: "memory");
       if (ct == 0) {
         float* gdst = dq_acc + ((size_t)(b * Hq + h) * nqt + qi) * (FB_QT * 128);
         asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(gdst),
@@ -530,17 +529,17 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
         tma_store_commit();
       }
     }
-    // ---- dV, dK epilogue ----
+    // ---- dV, dK epilogue: each thread converts 64 of the 128 columns of its row ----
     mbar_wait(bar + FbBars::acc_full, 0);
     tc_fence_after();
-    __nv_bfloat16* vrow = dqkv + (size_t)(kvrow0 + r) * ld + vcol;
-    __nv_bfloat16* krow = dqkv + (size_t)(kvrow0 + r) * ld + kcol;
+    __nv_bfloat16* vrow = dqkv + (size_t)(kvrow0 + r) * ld + vcol + hf * 64;
+    __nv_bfloat16* krow = dqkv + (size_t)(kvrow0 + r) * ld + kcol + hf * 64;
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
-      const uint32_t src = pass == 0 ? tm_dv : tm_dk;
+      const uint32_t src = (pass == 0 ? tm_dv : tm_dk) + hf * 64;
       __nv_bfloat16* drow = pass == 0 ? vrow : krow;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t v[32];
         tmem_ld_32x32(src + lane_off + c * 32, v);
         tmem_ld_wait();
