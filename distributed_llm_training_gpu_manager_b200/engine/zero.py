@@ -147,8 +147,15 @@ class ZeroEngine:
         self.fault_hooks: Dict[str, Callable] = {}
         self.fused = None
         self._symm: Dict[str, Any] = {}
-        self._want_fused = (comm == "fused" and self.on_cuda and self.world_size > 1
-                            and self.cfg.compute_dtype == torch.bfloat16)
+        # "auto" prefers the fused peer-memory kernels (the product) and falls back to NCCL (the baseline)
+        # when peers cannot be mapped (no P2P/IPC) or the dtype is not bf16
+        self._want_fused = (comm in ("fused", "auto") and self.on_cuda and self.world_size > 1
+                            and self.cfg.compute_dtype == torch.bfloat16
+                            and os.environ.get("B200ZERO_COMM", comm) != "nccl")
+        if self._want_fused and comm == "auto":
+            self._want_fused = self._probe_peer_memory()
+            if self._want_fused:
+                comm = self.comm_mode = "fused"
         self._in_backward = False
         self._reduce_now = True
         self._prefetch_evt: Dict[int, Any] = {}
@@ -199,6 +206,20 @@ class ZeroEngine:
             return full.reshape(-1)
         rows = spec.shape[0] // self.world_size
         return full[self.rank * rows:(self.rank + 1) * rows].reshape(-1)
+
+    def _probe_peer_memory(self) -> bool:
+        """Can every rank map every other rank's memory (CUDA IPC over NVLink)? Collective; all ranks
+        return the same answer."""
+        ok = 1
+        try:
+            from ..parallel.symm import SymmetricBuffer
+            probe = SymmetricBuffer(4096, device=self.device)
+            probe.close()
+        except Exception:
+            ok = 0
+        t = torch.tensor([ok], device=self.device, dtype=torch.int32)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item())
 
     def _zeros(self, numel: int, dtype: torch.dtype, name: str, symmetric: bool = False) -> torch.Tensor:
         """Device buffer; peer-mapped (CUDA IPC) when the fused backend will touch it from other ranks."""

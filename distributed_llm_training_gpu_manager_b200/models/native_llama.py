@@ -78,6 +78,64 @@ def hash_name(name: str) -> int:
     return h
 
 
+class ActivationOffloader:
+    """``activation_checkpointing.cpu_checkpointing`` (ref ``deepspeed_launcher.py:67,218``; on in the
+    reference's 70b preset): the tensors a block keeps for backward are copied to pinned host memory
+    on a side stream as soon as the block has produced them, and brought back one block ahead of the
+    backward pass, so HBM holds at most two blocks' worth of saved activations."""
+
+    def __init__(self, device: torch.device):
+        self.dev = device
+        self.stream = torch.cuda.Stream(device=device)
+        self.host: Dict[int, Dict[str, torch.Tensor]] = {}
+        self.meta: Dict[int, Dict[str, Any]] = {}
+        self.back: Dict[int, Tuple[Dict[str, Any], Any]] = {}
+        self._pool: Dict[Tuple, List[torch.Tensor]] = {}
+
+    def _pinned(self, like: torch.Tensor) -> torch.Tensor:
+        key = (tuple(like.shape), like.dtype)
+        free = self._pool.setdefault(key, [])
+        return free.pop() if free else torch.empty(like.shape, dtype=like.dtype, pin_memory=True)
+
+    def stash(self, l: int, tensors: Dict[str, Any]) -> None:
+        """Start the device->host copy of every tensor in ``tensors`` (non-tensors are kept as is)."""
+        self.stream.wait_stream(torch.cuda.current_stream())
+        host, meta = {}, {}
+        with torch.cuda.stream(self.stream):
+            for k, v in tensors.items():
+                if torch.is_tensor(v) and v.is_cuda:
+                    buf = self._pinned(v)
+                    buf.copy_(v, non_blocking=True)
+                    v.record_stream(self.stream)          # keep the device block alive until the copy ran
+                    host[k] = buf
+                else:
+                    meta[k] = v
+        self.host[l], self.meta[l] = host, meta
+
+    def prefetch(self, l: int) -> None:
+        if l in self.back or l not in self.host:
+            return
+        out = dict(self.meta[l])
+        with torch.cuda.stream(self.stream):
+            for k, buf in self.host[l].items():
+                out[k] = buf.to(self.dev, non_blocking=True)
+            evt = torch.cuda.Event()
+            evt.record(self.stream)
+        self.back[l] = (out, evt)
+
+    def fetch(self, l: int) -> Dict[str, Any]:
+        self.prefetch(l)
+        out, evt = self.back.pop(l)
+        torch.cuda.current_stream().wait_event(evt)
+        for t in out.values():
+            if torch.is_tensor(t) and t.is_cuda:
+                t.record_stream(torch.cuda.current_stream())
+        for k, buf in self.host.pop(l).items():
+            self._pool.setdefault((tuple(buf.shape), buf.dtype), []).append(buf)
+        self.meta.pop(l, None)
+        return out
+
+
 class NativeLlamaEngine(ZeroEngine):
     """ZeRO engine whose compute path is the hand-written kernel sequence above."""
 
@@ -111,6 +169,8 @@ class NativeLlamaEngine(ZeroEngine):
         self._ag_fused = (self.fused is not None and self.stage >= 3 and self.pooled_params
                           and os.environ.get("B200ZERO_AG_GEMM", "1") == "1")
         self._ag_ptrs: Dict[str, Any] = {}
+        self._act_offload = (ActivationOffloader(self.device)
+                             if (self.cfg.cpu_checkpointing and self.on_cuda) else None)
 
     # -------------------------------------------------------------- helpers
     def _w(self, layer: int, name: str) -> torch.Tensor:
@@ -247,6 +307,16 @@ class NativeLlamaEngine(ZeroEngine):
                 x, sv_l = self._block_fwd(l, x, keep=self.recompute != "full")
                 if sv_l is not None and self.recompute == "selective":
                     sv_l.pop("gu"); sv_l.pop("act")
+                if self._act_offload is not None:
+                    pack = dict(sv_l or {}, _x=ckpts[-1])
+                    actx = pack.pop("actx", None)
+                    if actx is not None and actx[0] == "native":      # (tag, qkv, out, lse, dims)
+                        pack.update(_qkv=actx[1], _lse=actx[3], _dims=actx[4])
+                    elif actx is not None:
+                        pack["actx"] = actx                            # sdpa autograd context stays on device
+                    self._act_offload.stash(l, pack)
+                    ckpts[-1] = None
+                    sv_l = {"_offloaded": True} if sv_l is not None else None
                 saved_acts.append(sv_l)
             hf, rstd_f, _ = E.rmsnorm_fwd(x, self.param_view("final_norm.weight"), c.norm_eps)
             # LM head + CE, chunked over tokens; gradients of the head are produced here
@@ -299,7 +369,17 @@ class NativeLlamaEngine(ZeroEngine):
                     evt = self._gslot_free_evt[(ui - 1) % 2]
                     if evt is not None:
                         torch.cuda.current_stream().wait_event(evt)
-                dx = self._block_bwd(l, sv["ckpts"][l], dx, acc, sv["acts"][l])
+                x_l, acts_l = sv["ckpts"][l], sv["acts"][l]
+                if self._act_offload is not None:
+                    pack = self._act_offload.fetch(l)
+                    if l - 1 >= 0:
+                        self._act_offload.prefetch(l - 1)
+                    x_l = pack.pop("_x")
+                    if acts_l is not None:
+                        if "_qkv" in pack:
+                            pack["actx"] = ("native", pack.pop("_qkv"), pack["attn"], pack.pop("_lse"), pack.pop("_dims"))
+                        acts_l = pack
+                dx = self._block_bwd(l, x_l, dx, acc, acts_l)
                 sv["ckpts"][l] = None
                 sv["acts"][l] = None
                 if self._reduce_now:

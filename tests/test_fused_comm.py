@@ -171,3 +171,43 @@ def test_fused_matches_nccl_on_real_gpus(stage):
         assert out["fused"][0] == pytest.approx(out["nccl"][0], rel=2e-3)
         assert out["fused"][1] == pytest.approx(out["nccl"][1], rel=2e-2)
         assert torch.allclose(out["fused"][2], out["nccl"][2], rtol=2e-2, atol=2e-3)
+
+
+def _module_fused_vs_nccl_rank(rank, world, stage):
+    """Generic nn.Module path (GPT-2, BASELINE.json config 2 shape): autograd writes into peer-mapped
+    gradient buckets, the fused reduce-scatter / Adam-push kernels replace NCCL."""
+    import torch.distributed as dist
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.engine import initialize
+    from distributed_llm_training_gpu_manager_b200.models import build_torch_model, get_config
+    torch.cuda.set_device(rank)
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=stage, offload_optimizer="none", offload_param="none", bf16_enabled=True, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=4, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+        stage3_param_persistence_threshold=1000, wall_clock_breakdown=False))
+    mc = get_config("gpt2-tiny")
+    out = {}
+    for comm in ("nccl", "fused"):
+        torch.manual_seed(11)
+        eng = initialize(build_torch_model(mc), ds, device=torch.device("cuda", rank), comm=comm)
+        assert eng.comm_mode == comm
+        g = torch.Generator().manual_seed(200 + rank)
+        losses = []
+        for _ in range(4):
+            ids = torch.randint(0, mc.vocab_size, (4, 64), generator=g).cuda()
+            eng.backward(eng(ids, ids))
+            losses.append(eng.step()["loss"])
+        out[comm] = (losses, eng.full_param("blocks.0.attn_qkv.weight").float().cpu())
+        if eng.fused is not None:
+            torch.cuda.synchronize(); dist.barrier(); eng.fused.close()
+    return out
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("stage", [1, 2])
+def test_module_path_fused_matches_nccl(stage):
+    from dist_utils import run_ranks_nccl
+    world = min(torch.cuda.device_count(), 4)
+    for out in run_ranks_nccl(_module_fused_vs_nccl_rank, world, (stage,)):
+        assert out["fused"][0] == pytest.approx(out["nccl"][0], rel=5e-3)
+        assert torch.allclose(out["fused"][1], out["nccl"][1], rtol=3e-2, atol=3e-3)

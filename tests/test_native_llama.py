@@ -64,3 +64,25 @@ def test_native_loss_decreases_and_skips_nonfinite():
     eng.fault_hooks["post_backward"] = lambda e: e.shard_grads.__setitem__(0, float("nan"))
     m = eng.train_step(ids, ids)
     assert m["nonfinite"] and torch.equal(before, eng.master)        # predicated update: nothing moved
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("recompute", ["selective", "full", "none"])
+def test_cpu_checkpointing_offloads_and_matches(recompute):
+    """activation_checkpointing.cpu_checkpointing: saved activations live in pinned host memory
+    between forward and backward; results must not change."""
+    def ds(cpu):
+        return DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+            zero_stage=3, offload_optimizer="none", offload_param="none", fp16_enabled=False, bf16_enabled=True,
+            train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+            cpu_checkpointing=cpu, wall_clock_breakdown=False))
+    mc = get_config("llama-tiny")
+    a = NativeLlamaEngine(mc, ds(False), seq_len=256, device=torch.device("cuda", 0), recompute=recompute)
+    b = NativeLlamaEngine(mc, ds(True), seq_len=256, device=torch.device("cuda", 0), recompute=recompute)
+    assert b._act_offload is not None and a._act_offload is None
+    g = torch.Generator().manual_seed(0)
+    for _ in range(3):
+        ids = torch.randint(0, mc.vocab_size, (2, 256), generator=g).cuda()
+        ma, mb = a.train_step(ids, ids), b.train_step(ids, ids)
+        assert ma["loss"] == pytest.approx(mb["loss"], rel=2e-3)
+        assert ma["grad_norm"] == pytest.approx(mb["grad_norm"], rel=2e-2)
