@@ -302,9 +302,8 @@ constexpr int FB_STAGE_F32 = FB_QT * 128 * 4;   // 32 KB dQ staging
 constexpr int FB_SMEM = 2 * FB_KV_BYTES + 4 * FB_Q_BYTES + 2 * FB_PT_BYTES + FB_STAGE_F32 + 2 * 2 * FB_QT * 4 + 256 + 1024;
 
 struct FbBars {
-  static constexpr int kv_full = 0, qdo_full = 8, qdo_empty = 24, st_full = 40 /*x2*/, dp_full = 56 /*x2*/,
-                       pt_ready = 72, dst_ready = 80, dq_full = 88, sdp_empty = 96, dqt_empty = 104, acc_full = 112,
-                       tmem_slot = 120;
+  static constexpr int kv_full = 0, qdo_full = 8, qdo_empty = 24, st_full = 40, dp_full = 48, pt_ready = 56,
+                       dst_ready = 64, dq_full = 72, sdp_empty = 80, dqt_empty = 88, acc_full = 96, tmem_slot = 104;
 };
 
 __global__ void __launch_bounds__(FB_THREADS, 1)
@@ -349,10 +348,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       mbar_init(bar + FbBars::qdo_full + 8 * i, 1);
       mbar_init(bar + FbBars::qdo_empty + 8 * i, 1);
     }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(bar + FbBars::st_full + 8 * i, 1);
-      mbar_init(bar + FbBars::dp_full + 8 * i, 1);
-    }
+    mbar_init(bar + FbBars::st_full, 1);
+    mbar_init(bar + FbBars::dp_full, 1);
     mbar_init(bar + FbBars::pt_ready, 256);
     mbar_init(bar + FbBars::dst_ready, 256);
     mbar_init(bar + FbBars::dq_full, 1);
@@ -368,9 +365,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
   tc_fence_after();
   uint32_t tmem;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(bar + FbBars::tmem_slot));
-  // TMEM columns: S^T[2] 0/64 (dQ^T of tile `it` reuses S^T[it&1] once it has been consumed), dP^T[2] 128/192,
-  // dV 256..383, dK 384..511.
-  const uint32_t tm_st0 = tmem, tm_dp0 = tmem + 128, tm_dv = tmem + 256, tm_dk = tmem + 384;
+  const uint32_t tm_st = tmem, tm_dp = tmem + 64, tm_dv = tmem + 128, tm_dk = tmem + 256, tm_dq = tmem + 384;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -398,52 +393,40 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       constexpr uint32_t id_acc = umma_idesc_bf16(128, 128, false, true);    // dV, dK
       constexpr uint32_t id_dq = umma_idesc_bf16(128, FB_QT, true, true);    // dQ^T
       mbar_wait(bar + FbBars::kv_full, 0);
-      // S^T and dP^T of tile `t` (issued one tile ahead of the accumulating GEMMs: software pipeline)
-      auto issue_scores = [&](int t) {
-        const int st = t & 1;
-        const uint32_t ph = (t >> 1) & 1;
+      for (int it = 0; it < iters; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1, par = it & 1;
         const uint32_t qb = q_s + st * FB_Q_BYTES, dob = do_s + st * FB_Q_BYTES;
         mbar_wait(bar + FbBars::qdo_full + 8 * st, ph);
-        if (t >= 2) {
-          // Buffers [t&1] were last used by tile t-2. Its S^T/dP^T have been read: every compute thread
-          // arrives on sdp_empty *before* dst_ready(t-2), which this warp has already waited for — so no
-          // wait on sdp_empty here (and waiting on it would race with the next phase's arrivals).
-          // Its dQ^T, which lives in the S^T columns, must have been drained:
-          mbar_wait(bar + FbBars::dqt_empty, (uint32_t)(t - 2) & 1u);
-        }
+        mbar_wait(bar + FbBars::sdp_empty, par ^ 1u);       // S^T / dP^T columns drained by the previous tile
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          umma_f16<1>(tm_st0 + st * 64, umma_smem_desc_sw128(k_s + (k >> 2) * FB_KV_HALF + (k & 3) * 32, 16, 1024),
+          umma_f16<1>(tm_st, umma_smem_desc_sw128(k_s + (k >> 2) * FB_KV_HALF + (k & 3) * 32, 16, 1024),
                       umma_smem_desc_sw128(qb + (k >> 2) * FB_Q_HALF + (k & 3) * 32, 16, 1024), id_s, k != 0);
-        umma_commit<1>(bar + FbBars::st_full + 8 * st);
+        umma_commit<1>(bar + FbBars::st_full);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          umma_f16<1>(tm_dp0 + st * 64, umma_smem_desc_sw128(v_s + (k >> 2) * FB_KV_HALF + (k & 3) * 32, 16, 1024),
+          umma_f16<1>(tm_dp, umma_smem_desc_sw128(v_s + (k >> 2) * FB_KV_HALF + (k & 3) * 32, 16, 1024),
                       umma_smem_desc_sw128(dob + (k >> 2) * FB_Q_HALF + (k & 3) * 32, 16, 1024), id_s, k != 0);
-        umma_commit<1>(bar + FbBars::dp_full + 8 * st);
-      };
-      issue_scores(0);
-      for (int it = 0; it < iters; ++it) {
-        const int st = it & 1;
-        const uint32_t par = it & 1;
-        const uint32_t qb = q_s + st * FB_Q_BYTES, dob = do_s + st * FB_Q_BYTES;
+        umma_commit<1>(bar + FbBars::dp_full);
         mbar_wait(bar + FbBars::pt_ready, par);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < 4; ++k)                          // dV += P^T dO
           umma_f16<1>(tm_dv, umma_smem_desc_sw128(pt_s + k * 32, 16, 1024),
                       umma_smem_desc_sw128(dob + k * 2048, FB_Q_HALF, 1024), id_acc, (it | k) != 0);
-        if (it + 1 < iters) issue_scores(it + 1);            // tensor core stays busy while dS^T is being formed
         mbar_wait(bar + FbBars::dst_ready, par);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < 4; ++k)                          // dK += dS^T Q
           umma_f16<1>(tm_dk, umma_smem_desc_sw128(dst_s + k * 32, 16, 1024),
                       umma_smem_desc_sw128(qb + k * 2048, FB_Q_HALF, 1024), id_acc, (it | k) != 0);
+        mbar_wait(bar + FbBars::dqt_empty, par ^ 1u);        // previous dQ^T tile read out of TMEM
+        tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < 8; ++k)                          // dQ^T = K^T dS^T  (into the consumed S^T columns)
-          umma_f16<1>(tm_st0 + st * 64, umma_smem_desc_sw128(k_s + k * 2048, FB_KV_HALF, 1024),
+        for (int k = 0; k < 8; ++k)                          // dQ^T = K^T dS^T
+          umma_f16<1>(tm_dq, umma_smem_desc_sw128(k_s + k * 2048, FB_KV_HALF, 1024),
                       umma_smem_desc_sw128(dst_s + k * 2048, FB_KV_HALF, 1024), id_dq, k != 0);
         umma_commit<1>(bar + FbBars::qdo_empty + 8 * st);
         umma_commit<1>(bar + FbBars::dq_full);
@@ -470,9 +453,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       const bool diag = q_pos0 < j * 128 + 128;
       const int c0 = hf * 32;                                // first query column of this thread
       // ---- P^T ----
-      const uint32_t bph = (it >> 1) & 1;                    // phase of the per-buffer barriers
-      const uint32_t tm_st = tm_st0 + (it & 1) * 64, tm_dp = tm_dp0 + (it & 1) * 64, tm_dq = tm_st;
-      mbar_wait(bar + FbBars::st_full + 8 * (it & 1), bph);
+      mbar_wait(bar + FbBars::st_full, par);
       tc_fence_after();
       uint32_t pk[16];                                       // 32 probabilities as packed bf16
       {
@@ -499,7 +480,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       fence_proxy_async_smem();
       mbar_arrive(bar + FbBars::pt_ready);
       // ---- dS^T = P^T * (dP^T - Delta) * scale ----
-      mbar_wait(bar + FbBars::dp_full + 8 * (it & 1), bph);
+      mbar_wait(bar + FbBars::dp_full, par);
       tc_fence_after();
       uint32_t dk_[16];
       {

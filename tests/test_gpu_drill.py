@@ -1,0 +1,48 @@
+"""BASELINE.json config 4 on real GPUs (tiny Llama, native kernels, fused collectives): a rank is
+SIGKILLed (spot preemption of one worker) and later a NaN gradient is injected; the supervisor
+relaunches, workers resume from the newest verified checkpoint, the non-finite step is skipped on
+the device, detected, rolled back and training finishes."""
+import json
+import os
+
+import pytest
+import torch
+
+from distributed_llm_training_gpu_manager_b200.ai_engine import (DeepSpeedConfig, DeepSpeedLauncher, OffloadDevice,
+                                                                  ZeROStage)
+
+from dist_utils import free_port
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+def test_kill_nan_rollback_resume_on_gpus(tmp_path):
+    n = min(torch.cuda.device_count(), 4)
+    cfg = DeepSpeedConfig(model_name="llama_tiny", zero_stage=ZeROStage.FULL_PARTITIONING,
+                          offload_optimizer=OffloadDevice.NONE, offload_param=OffloadDevice.NONE, fp16_enabled=False,
+                          bf16_enabled=True, train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1,
+                          learning_rate=1e-3, warmup_steps=3, total_training_steps=200, num_gpus=n,
+                          master_port=free_port(), stage3_param_persistence_threshold=1000,
+                          wall_clock_breakdown=False)
+    launcher = DeepSpeedLauncher()
+    result_file = tmp_path / "result.json"
+    env_backup = dict(os.environ)
+    os.environ.update(B200ZERO_KILL_RANK_AT="9:1", B200ZERO_INJECT_NAN_GRAD_AT="17", MASTER_ADDR="127.0.0.1",
+                      B200ZERO_MAX_RESTARTS="2")
+    try:
+        res = launcher.launch(cfg, "builtin:llama-tiny",
+                              ["--steps=24", f"--save_dir={tmp_path / 'ckpt'}", "--save_every=4",
+                               f"--result={result_file}", "--seq_len=256", "--window=20", "--engine=native"])
+        rec = launcher.registry.wait(res.job_id, timeout=500)
+    finally:
+        os.environ.clear(); os.environ.update(env_backup)
+    log = launcher.registry.tail(res.job_id) or ""
+    assert rec is not None and rec.returncode == 0, log[-3000:]
+    assert "restart 1/2" in log and "resumed from global_step8" in log, log[-3000:]
+    out = json.loads(result_file.read_text())
+    assert out["status"] == "finished" and out["final_step"] == 24
+    assert "divergence" in out["alerts"] and out["rollbacks"] == 1, out
+    assert out["halt_latency_ms"] and out["halt_latency_ms"][0] < 50
+    (tmp_path / "drill_result.json").write_text(json.dumps(out))
+    print("DRILL", json.dumps({"halt_latency_ms": out["halt_latency_ms"], "rollbacks": out["rollbacks"],
+                               "steps_run": out["steps_run"]}))
