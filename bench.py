@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--attn", default=None, help="attention backend override: native | sdpa")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--breakdown", action="store_true", help="after the timed region, run one extra step with per-phase CUDA-event timers")
+    ap.add_argument("--torch-profile", default=None, help="write a per-kernel CUDA-time table of one extra step to this file (rank 0)")
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model (result is not a bench value)")
     return ap.parse_args()
 
@@ -234,6 +235,16 @@ def run_ours(args) -> int:
         engine.timers.enabled = False
         engine.cfg.wall_clock_breakdown = False
 
+    if args.torch_profile:
+        from torch.profiler import ProfilerActivity, profile
+        sync_all()
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            engine.train_step(*dev[0])
+            sync_all()
+        if rank == 0:
+            with open(args.torch_profile, "w") as f:
+                f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))
+
     # ---- max over ranks ----
     t = torch.tensor([ms_total, e2e_ms or 0.0], device=device, dtype=torch.float64)
     if world > 1:
@@ -263,6 +274,7 @@ def run_ours(args) -> int:
         "model_tflops_per_gpu": round(per_gpu_tflops, 1),
         "mfu_vs_measured_cublas_sustained": round(per_gpu_tflops / peaks.get("bf16_tflops_sustained", 1358.3), 3),
         "final_loss": last["loss"] if last else None,
+        "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 1),
     }
     if breakdown is not None:
         out["breakdown_ms"] = {k: round(v, 2) for k, v in breakdown.items()}
