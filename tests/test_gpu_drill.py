@@ -38,7 +38,11 @@ def test_kill_nan_rollback_resume_on_gpus(tmp_path):
         os.environ.clear(); os.environ.update(env_backup)
     log = launcher.registry.tail(res.job_id) or ""
     assert rec is not None and rec.returncode == 0, log[-3000:]
-    assert "restart 1/2" in log and "resumed from global_step8" in log, log[-3000:]
+    # steps take a few ms here, so the asynchronous write of step 8 may not have been completed and
+    # verified when the rank died at step 9: the newest *verified* tag (4 or 8) must be the one used
+    import re
+    m = re.search(r"resumed from global_step(\d+)", log)
+    assert "restart 1/2" in log and m and int(m.group(1)) in (4, 8), log[-3000:]
     out = json.loads(result_file.read_text())
     assert out["status"] == "finished" and out["final_step"] == 24
     assert "divergence" in out["alerts"] and out["rollbacks"] == 1, out
