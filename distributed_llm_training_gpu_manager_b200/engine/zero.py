@@ -426,7 +426,8 @@ class ZeroEngine:
                     else:
                         dist.all_reduce(gr)
                         dst.add_(gr.to(dst.dtype), alpha=scale)
-            gb.zero_()
+            if getattr(self, "_zero_after_reduce", True):
+                gb.zero_()         # autograd accumulates in place; the native executor overwrites instead
             if use_side and self.pooled_grads and ui >= 1:
                 evt = torch.cuda.Event()
                 evt.record(self.comm_stream)

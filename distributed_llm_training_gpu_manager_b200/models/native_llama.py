@@ -160,10 +160,16 @@ class NativeLlamaEngine(ZeroEngine):
         #   selective — keep everything except the two largest tensors (gate|up and silu·up, 0.7 GB per
         #               block at 8k tokens) and recompute just that GEMM + SwiGLU; default when the
         #               config enables activation checkpointing (180 GB HBM3e leaves room for the rest)
+        #   light     — keep everything except silu·up; backward re-runs only the SwiGLU kernel
         #   none      — keep everything (config has no activation_checkpointing block)
+        #   auto      — (default with activation checkpointing) `light` when the free HBM after building
+        #               the engine covers it with a 12 GB margin, else `selective`
         import os as _os
-        self.recompute = recompute or _os.environ.get("B200ZERO_RECOMPUTE") or ("selective" if self.cfg.act_ckpt else "none")
-        assert self.recompute in ("full", "selective", "none")
+        self.recompute = recompute or _os.environ.get("B200ZERO_RECOMPUTE") or ("auto" if self.cfg.act_ckpt else "none")
+        assert self.recompute in ("full", "selective", "light", "none", "auto")
+        if self.recompute == "auto":
+            self.recompute = self._pick_recompute_policy()
+        self._zero_after_reduce = False     # every gradient is overwritten by its producer (see _reduce_unit)
         # K2: with the fused backend at ZeRO-3 every forward GEMM gathers its own weight in-kernel
         import os
         self._ag_fused = (self.fused is not None and self.stage >= 3 and self.pooled_params
@@ -171,6 +177,25 @@ class NativeLlamaEngine(ZeroEngine):
         self._ag_ptrs: Dict[str, Any] = {}
         self._act_offload = (ActivationOffloader(self.device)
                              if (self.cfg.cpu_checkpointing and self.on_cuda) else None)
+
+    def _pick_recompute_policy(self) -> str:
+        if not self.on_cuda:
+            return "selective"
+        c = self.mcfg
+        T = self.cfg.micro_batch * self.seq_len
+        qkv = (c.n_heads + 2 * c.n_kv_heads) * c.head_dim
+        per_layer_sel = T * (5 * c.hidden + qkv) * 2            # h1, attn, x1, h2, x (ckpt) + qkv, bf16
+        per_layer_gu = T * 2 * c.ffn * 2
+        work = T * (2 * c.ffn * 3 + 4 * c.hidden) * 2 + self.head_chunk * c.padded_vocab * 2 * 2
+        need_light = c.n_layers * (per_layer_sel + per_layer_gu) + work
+        free = torch.cuda.mem_get_info(self.device)[0] + (torch.cuda.memory_reserved(self.device)
+                                                         - torch.cuda.memory_allocated(self.device))
+        choice = "light" if free - need_light > 12 * 2 ** 30 else "selective"
+        if self.world_size > 1:                                  # all ranks must run the same kernel sequence
+            t = torch.tensor([1 if choice == "light" else 0], device=self.device, dtype=torch.int32)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            choice = "light" if int(t.item()) == 1 else "selective"
+        return choice
 
     # -------------------------------------------------------------- helpers
     def _w(self, layer: int, name: str) -> torch.Tensor:
@@ -260,6 +285,7 @@ class NativeLlamaEngine(ZeroEngine):
             self._begin_block_bwd(l)
             if "gu" not in sv:                                        # selective: redo gate|up GEMM + SwiGLU only
                 sv["gu"] = G.linear_fwd(sv["h2"], self._w(l, "w_gate_up"))
+            if "act" not in sv:                                       # light: SwiGLU only
                 sv["act"] = E.swiglu_fwd(sv["gu"])
         adt = dict(accumulate=acc)
         # MLP
@@ -307,6 +333,8 @@ class NativeLlamaEngine(ZeroEngine):
                 x, sv_l = self._block_fwd(l, x, keep=self.recompute != "full")
                 if sv_l is not None and self.recompute == "selective":
                     sv_l.pop("gu"); sv_l.pop("act")
+                elif sv_l is not None and self.recompute == "light":
+                    sv_l.pop("act")
                 if self._act_offload is not None:
                     pack = dict(sv_l or {}, _x=ckpts[-1])
                     actx = pack.pop("actx", None)
@@ -384,6 +412,8 @@ class NativeLlamaEngine(ZeroEngine):
                 sv["acts"][l] = None
                 if self._reduce_now:
                     self._reduce_unit(ui)
+            if not acc:
+                self.grad_view("embed.weight").zero_()               # scatter-add target; everything else is overwritten
             E.embedding_bwd(sv["ids"], dx, self.grad_view("embed.weight"))
             if self._reduce_now:
                 self._reduce_unit(0)
