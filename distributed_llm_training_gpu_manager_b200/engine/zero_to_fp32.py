@@ -1,0 +1,59 @@
+#!/usr/bin/env python
+"""Consolidate a ZeRO checkpoint written by this framework into one fp32 ``state_dict`` file —
+the counterpart of DeepSpeed's ``zero_to_fp32.py`` (which it copies next to every checkpoint; the
+reference promises those files but never writes any). This copy understands the
+row-partition layout recorded under ``b200zero_layout`` in the shard files and needs only torch.
+
+    python zero_to_fp32.py <checkpoint_dir> <output.pt> [--tag global_step100]
+"""
+import argparse
+import json
+import sys
+from pathlib import Path
+
+import torch
+
+
+def consolidate(ckpt_dir: str, tag: str = None):
+    root = Path(ckpt_dir)
+    tag = tag or (root / "latest").read_text().strip()
+    tdir = root / tag
+    manifest = json.loads((tdir / "manifest.json").read_text())
+    ws = manifest["world_size"]
+    shards = []
+    for r in range(ws):
+        hits = sorted(tdir.glob(f"*zero_pp_rank_{r}_mp_rank_00_optim_states.pt"))
+        if not hits:
+            raise FileNotFoundError(f"optimizer shard of rank {r} missing in {tdir}")
+        shards.append(torch.load(hits[0], map_location="cpu", weights_only=False))
+    layout = shards[0]["b200zero_layout"]
+    flats = []
+    for sd in shards:
+        osd = sd["optimizer_state_dict"]
+        flats.append((osd.get("fp32_flat_groups") or osd.get("single_partition_of_fp32_groups"))[0])
+    out = {}
+    for unit in layout["units"]:
+        for p in unit["params"]:
+            off, n, shape = p["shard_offset"], p["shard_numel"], tuple(p["shape"])
+            if p["partitioned"]:
+                rows = [flats[r][off:off + n].view((shape[0] // ws,) + shape[1:]) for r in range(ws)]
+                out[p["name"]] = torch.cat(rows, 0).clone()
+            else:
+                out[p["name"]] = flats[0][off:off + n].view(shape).clone()
+    return out, tag
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("checkpoint_dir")
+    ap.add_argument("output_file")
+    ap.add_argument("--tag", default=None)
+    ns = ap.parse_args(argv)
+    sd, tag = consolidate(ns.checkpoint_dir, ns.tag)
+    torch.save(sd, ns.output_file)
+    print(f"{tag}: wrote {len(sd)} tensors ({sum(t.numel() for t in sd.values()) / 1e6:.1f} M parameters) to {ns.output_file}")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

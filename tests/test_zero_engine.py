@@ -203,3 +203,33 @@ def test_supervisor_restarts_after_rank_kill_and_resumes(tmp_path):
     # the NaN gradient injected at step 23 (after the restart) was caught, the update skipped, and
     # the run rolled back to the last good checkpoint and carried on
     assert "divergence" in out["alerts"] and out["rollbacks"] == 1, out
+
+
+def test_zero_to_fp32_consolidates_all_ranks(tmp_path):
+    from distributed_llm_training_gpu_manager_b200.engine.zero_to_fp32 import consolidate
+    run_ranks(_ckpt_rank, 2, (3, str(tmp_path)))
+    sd, tag = consolidate(str(tmp_path))
+    assert tag == "global_step3" and (tmp_path / "zero_to_fp32.py").exists()
+    ref = build_torch_model(get_config("gpt2-tiny")).state_dict()
+    assert set(sd) == {k for k in ref if not k.endswith("lm_head.weight")} or set(sd) <= set(ref)
+    for k, v in sd.items():
+        assert v.shape == ref[k].shape and v.dtype == torch.float32
+
+
+def test_user_script_through_native_launcher(tmp_path):
+    """examples/train_gpt2.py launched the way the reference launches a DeepSpeed script."""
+    cfg = DeepSpeedConfig(model_name="ex", zero_stage=ZeROStage.GRADIENT_PARTITIONING, offload_optimizer=OffloadDevice.NONE,
+                          offload_param=OffloadDevice.NONE, fp16_enabled=False, train_micro_batch_size_per_gpu=2,
+                          gradient_accumulation_steps=2, num_gpus=2, master_port=free_port(), wall_clock_breakdown=False)
+    launcher = DeepSpeedLauncher()
+    script = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples", "train_gpt2.py")
+    env_backup = dict(os.environ)
+    os.environ.update(B200ZERO_BACKEND="gloo", MASTER_ADDR="127.0.0.1")
+    try:
+        res = launcher.launch(cfg, script, ["--steps", "12"])
+        rec = launcher.registry.wait(res.job_id, timeout=300)
+    finally:
+        os.environ.clear(); os.environ.update(env_backup)
+    log = launcher.registry.tail(res.job_id) or ""
+    assert rec is not None and rec.returncode == 0, log
+    assert "step 10 loss" in log
