@@ -342,7 +342,30 @@ pull_allgather_kernel(const __grid_constant__ PeerTable pt, const Segment* __res
   }
 }
 
+// The communication kernels are meant to share SMs with a persistent GEMM CTA that needs ~200 KB of
+// shared memory. An SM's L1/shared split can only change while the SM is idle, so a comm CTA that
+// got there first with the default (L1-heavy) carveout would keep the GEMM CTA off that SM until it
+// exits — and with a statically partitioned persistent GEMM that doubles the GEMM's run time
+// (measured: 723 instead of 1400 TFLOP/s on the first GEMM of every backward block). Asking for
+// the max-shared carveout makes the two kernels co-resident whichever arrives first.
+template <typename K>
+static void prefer_max_shared_carveout(K kernel) {
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+static void comm_kernels_setup_once() {
+  static bool done = false;
+  if (done) return;
+  prefer_max_shared_carveout(fused_reduce_scatter_kernel<true>);
+  prefer_max_shared_carveout(fused_reduce_scatter_kernel<false>);
+  prefer_max_shared_carveout(fused_adam_push_kernel<true>);
+  prefer_max_shared_carveout(fused_adam_push_kernel<false>);
+  prefer_max_shared_carveout(pull_allgather_kernel);
+  prefer_max_shared_carveout(fold_partials_kernel);
+  done = true;
+}
+
 static int fill_table(PeerTable& pt, void* const* data_ptrs, void* const* signal_ptrs, int ws) {
+  comm_kernels_setup_once();
   BZ_REQUIRE(ws >= 1 && ws <= MAX_WS, "fused comm: world size %d not in [1, %d]", ws, MAX_WS);
   for (int i = 0; i < MAX_WS; ++i) {
     pt.data[i] = i < ws ? data_ptrs[i] : nullptr;
