@@ -71,6 +71,39 @@ class LlamaParams(ParamSource):
         return out
 
 
+def activation_bytes(c: ModelConfig, micro_batch: int, seq_len: int, head_chunk: int = 2048) -> Dict[str, int]:
+    """bf16 bytes of activations alive at the forward/backward turn-around, per recompute policy."""
+    T = micro_batch * seq_len
+    qkv = (c.n_heads + 2 * c.n_kv_heads) * c.head_dim
+    ckpt = T * c.hidden * 2                                       # block input
+    sel = T * (4 * c.hidden + qkv) * 2 + ckpt                     # + h1, attn, x1, h2, qkv
+    gu = T * 2 * c.ffn * 2
+    act = T * c.ffn * 2
+    work = T * (2 * c.ffn * 3 + 6 * c.hidden + 2 * qkv) * 2 + head_chunk * c.padded_vocab * 2 * 2 + T * c.hidden * 4
+    L = c.n_layers
+    return {"full": L * ckpt + work + sel + gu + act, "selective": L * sel + work + gu + act,
+            "light": L * (sel + gu) + work + act, "none": L * (sel + gu + act) + work}
+
+
+def static_bytes(c: ModelConfig, world_size: int, stage: int = 3, offload_optimizer: bool = False,
+                 grad_bytes: int = 2) -> Dict[str, float]:
+    """Per-GPU bytes of the engine's persistent buffers (ZeRO-3 native path), for capacity planning
+    against 180 GB of HBM3e (BASELINE.json config 5: Llama-3-70B on 8 × B200)."""
+    d, hd = c.hidden, c.head_dim
+    qkv = (c.n_heads + 2 * c.n_kv_heads) * hd
+    block = d * (qkv + d) + 3 * d * c.ffn + 2 * d
+    root = 2 * c.padded_vocab * d + d
+    total = c.n_layers * block + root
+    shard = total / max(world_size, 1) if stage >= 1 else total
+    out = {"optimizer_states": 0.0 if offload_optimizer else 12.0 * shard, "param_shard": 2.0 * shard,
+           "grad_shard": float(grad_bytes) * shard,
+           "param_buffers": 2.0 * (2 * block + root) if stage >= 3 else 2.0 * total,
+           "grad_buffers": 2.0 * (2 * block + root) if stage >= 2 else 2.0 * total,
+           "host_pinned": 12.0 * shard if offload_optimizer else 0.0, "params_total": float(total)}
+    out["device_total"] = sum(v for k, v in out.items() if k not in ("host_pinned", "params_total"))
+    return out
+
+
 def hash_name(name: str) -> int:
     h = 2166136261
     for ch in name.encode():
@@ -179,23 +212,20 @@ class NativeLlamaEngine(ZeroEngine):
                              if (self.cfg.cpu_checkpointing and self.on_cuda) else None)
 
     def _pick_recompute_policy(self) -> str:
+        """Cheapest-recompute policy whose saved activations fit in the HBM left after the engine's
+        static buffers, with a 12 GB margin: light → selective → full."""
         if not self.on_cuda:
             return "selective"
-        c = self.mcfg
-        T = self.cfg.micro_batch * self.seq_len
-        qkv = (c.n_heads + 2 * c.n_kv_heads) * c.head_dim
-        per_layer_sel = T * (5 * c.hidden + qkv) * 2            # h1, attn, x1, h2, x (ckpt) + qkv, bf16
-        per_layer_gu = T * 2 * c.ffn * 2
-        work = T * (2 * c.ffn * 3 + 4 * c.hidden) * 2 + self.head_chunk * c.padded_vocab * 2 * 2
-        need_light = c.n_layers * (per_layer_sel + per_layer_gu) + work
+        need = activation_bytes(self.mcfg, self.cfg.micro_batch, self.seq_len, self.head_chunk)
         free = torch.cuda.mem_get_info(self.device)[0] + (torch.cuda.memory_reserved(self.device)
                                                          - torch.cuda.memory_allocated(self.device))
-        choice = "light" if free - need_light > 12 * 2 ** 30 else "selective"
+        order = ["light", "selective", "full"]
+        pick = next((i for i, p in enumerate(order) if free - need[p] > 12 * 2 ** 30), len(order) - 1)
         if self.world_size > 1:                                  # all ranks must run the same kernel sequence
-            t = torch.tensor([1 if choice == "light" else 0], device=self.device, dtype=torch.int32)
-            dist.all_reduce(t, op=dist.ReduceOp.MIN)
-            choice = "light" if int(t.item()) == 1 else "selective"
-        return choice
+            t = torch.tensor([pick], device=self.device, dtype=torch.int32)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            pick = int(t.item())
+        return order[pick]
 
     # -------------------------------------------------------------- helpers
     def _w(self, layer: int, name: str) -> torch.Tensor:

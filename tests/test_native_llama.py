@@ -86,3 +86,22 @@ def test_cpu_checkpointing_offloads_and_matches(recompute):
         ma, mb = a.train_step(ids, ids), b.train_step(ids, ids)
         assert ma["loss"] == pytest.approx(mb["loss"], rel=2e-3)
         assert ma["grad_norm"] == pytest.approx(mb["grad_norm"], rel=2e-2)
+
+
+def test_capacity_planning_70b_on_8_b200():
+    """BASELINE.json config 5 sizing: Llama-3-70B ZeRO-3 on 8 x 180 GB — what fits where."""
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import activation_bytes, static_bytes
+    GB = 2 ** 30
+    c70, c8 = get_config("llama3-70b"), get_config("llama3-8b")
+    st = static_bytes(c70, 8)
+    assert 69e9 < st["params_total"] < 72e9
+    assert 140 * GB < st["device_total"] < 170 * GB          # fits in 180 GB with all state on the GPU ...
+    act = activation_bytes(c70, 1, 4096)
+    assert st["device_total"] + act["full"] < 178 * GB       # ... only with full recompute
+    assert st["device_total"] + act["selective"] > 178 * GB
+    off = static_bytes(c70, 8, offload_optimizer=True)       # host offload moves 12 B/param off the GPU
+    assert off["device_total"] < 60 * GB and off["host_pinned"] > 95 * GB
+    assert off["device_total"] + act["light"] < 178 * GB
+    # the 8B headline config: one GPU holds everything, light recompute fits (measured peak 153 GB)
+    s8, a8 = static_bytes(c8, 1), activation_bytes(c8, 2, 4096)
+    assert 120 * GB < s8["device_total"] < 140 * GB and s8["device_total"] + a8["light"] < 172 * GB
