@@ -299,7 +299,7 @@ constexpr int FB_Q_BYTES = FB_QT * 128 * 2;     // 16 KB, two halves of 8 KB
 constexpr int FB_Q_HALF = FB_QT * 64 * 2;
 constexpr int FB_PT_BYTES = 128 * FB_QT * 2;    // 16 KB
 constexpr int FB_STAGE_F32 = FB_QT * 128 * 4;   // 32 KB dQ staging
-constexpr int FB_SMEM = 2 * FB_KV_BYTES + 4 * FB_Q_BYTES + 2 * FB_PT_BYTES + FB_STAGE_F32 + 2 * 2 * FB_QT * 4 + 256 + 1024;
+constexpr int FB_SMEM = 2 * FB_KV_BYTES + 4 * FB_Q_BYTES + 2 * FB_PT_BYTES + 2 * FB_STAGE_F32 + 2 * 2 * FB_QT * 4 + 256 + 1024;
 
 struct FbBars {
   static constexpr int kv_full = 0, qdo_full = 8, qdo_empty = 24, st_full = 40, dp_full = 48, pt_ready = 56,
@@ -320,7 +320,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
   const uint32_t pt_s = do_s + 2 * FB_Q_BYTES;
   const uint32_t dst_s = pt_s + FB_PT_BYTES;
   const uint32_t stg_s = dst_s + FB_PT_BYTES;
-  const uint32_t stat_s = stg_s + FB_STAGE_F32;                   // [2 stages][lse 64 | delta 64] floats
+  const uint32_t stat_s = stg_s + 2 * FB_STAGE_F32;               // (staging is double-buffered) [2][lse 64 | delta 64] floats
   const uint32_t bar = stat_s + 2 * 2 * FB_QT * 4;
   float* stat = reinterpret_cast<float*>(smem_raw + (stat_s - smem_u32(smem_raw)));
   float* stg = reinterpret_cast<float*>(smem_raw + (stg_s - smem_u32(smem_raw)));
@@ -508,14 +508,14 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       // ---- dQ^T tile: TMEM -> fp32 staging [q][hd] -> bulk reduce-add into the workspace ----
       mbar_wait(bar + FbBars::dq_full, par);
       tc_fence_after();
-      if (ct == 0) tma_store_wait_read<0>();                 // previous bulk reduce finished reading staging
+      if (ct == 0) tma_store_wait_read<1>();                 // the reduce issued two tiles ago has read its staging buffer
       asm volatile("bar.sync 2, 256;" ::: "memory");
       {
         uint32_t v[32];
         tmem_ld_32x32(tm_dq + lane_off + c0, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 32; ++e) stg[(c0 + e) * 128 + r] = __uint_as_float(v[e]);
+        for (int e = 0; e < 32; ++e) stg[(it & 1) * (FB_QT * 128) + (c0 + e) * 128 + r] = __uint_as_float(v[e]);
       }
       tc_fence_before();
       mbar_arrive(bar + FbBars::dqt_empty);
@@ -524,7 +524,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_constant
       if (ct == 0) {
         float* gdst = dq_acc + ((size_t)(b * Hq + h) * nqt + qi) * (FB_QT * 128);
         asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(gdst),
-                     "r"(stg_s), "n"(FB_STAGE_F32)
+                     "r"(stg_s + (it & 1) * FB_STAGE_F32), "n"(FB_STAGE_F32)
                      : "memory");
         tma_store_commit();
       }

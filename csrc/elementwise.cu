@@ -236,19 +236,35 @@ __global__ void __launch_bounds__(EW_THREADS)
 swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ act, long long T, int F) {
   const int vecs = F >> 3;
   const long long items = T * vecs;
-  for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < items;
-       it += (long long)gridDim.x * blockDim.x) {
-    const long long t = it / vecs;
-    const int v = (int)(it - t * vecs);
-    float g[8], u[8], o[8];
-    load8(gu + t * 2 * F + v * 8, g);
-    load8(gu + t * 2 * F + F + v * 8, u);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  constexpr int UNR = 4;  // 8 independent 128-bit loads in flight per thread
+  for (long long it0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; it0 < items; it0 += stride * UNR) {
+    float g[UNR][8], u[UNR][8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const float sig = 1.f / (1.f + __expf(-g[e]));
-      o[e] = g[e] * sig * u[e];
+    for (int k = 0; k < UNR; ++k) {
+      const long long it = it0 + k * stride;
+      if (it < items) {
+        const long long t = it / vecs;
+        const int v = (int)(it - t * vecs);
+        load8(gu + t * 2 * F + v * 8, g[k]);
+        load8(gu + t * 2 * F + F + v * 8, u[k]);
+      }
     }
-    store8(act + t * F + v * 8, o);
+#pragma unroll
+    for (int k = 0; k < UNR; ++k) {
+      const long long it = it0 + k * stride;
+      if (it < items) {
+        const long long t = it / vecs;
+        const int v = (int)(it - t * vecs);
+        float o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float sig = 1.f / (1.f + __expf(-g[k][e]));
+          o[e] = g[k][e] * sig * u[k][e];
+        }
+        store8(act + t * F + v * 8, o);
+      }
+    }
   }
 }
 __global__ void __launch_bounds__(EW_THREADS)

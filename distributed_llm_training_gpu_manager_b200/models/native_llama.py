@@ -195,8 +195,8 @@ class NativeLlamaEngine(ZeroEngine):
         #               config enables activation checkpointing (180 GB HBM3e leaves room for the rest)
         #   light     — keep everything except silu·up; backward re-runs only the SwiGLU kernel
         #   none      — keep everything (config has no activation_checkpointing block)
-        #   auto      — (default with activation checkpointing) `light` when the free HBM after building
-        #               the engine covers it with a 12 GB margin, else `selective`
+        #   auto      — (default with activation checkpointing) the cheapest policy whose saved activations
+        #               fit in the HBM left after building the engine with a 12 GB margin
         import os as _os
         self.recompute = recompute or _os.environ.get("B200ZERO_RECOMPUTE") or ("auto" if self.cfg.act_ckpt else "none")
         assert self.recompute in ("full", "selective", "light", "none", "auto")
@@ -213,13 +213,13 @@ class NativeLlamaEngine(ZeroEngine):
 
     def _pick_recompute_policy(self) -> str:
         """Cheapest-recompute policy whose saved activations fit in the HBM left after the engine's
-        static buffers, with a 12 GB margin: light → selective → full."""
+        static buffers, with a 12 GB margin: none → light → selective → full."""
         if not self.on_cuda:
             return "selective"
         need = activation_bytes(self.mcfg, self.cfg.micro_batch, self.seq_len, self.head_chunk)
         free = torch.cuda.mem_get_info(self.device)[0] + (torch.cuda.memory_reserved(self.device)
                                                          - torch.cuda.memory_allocated(self.device))
-        order = ["light", "selective", "full"]
+        order = ["none", "light", "selective", "full"]
         pick = next((i for i, p in enumerate(order) if free - need[p] > 12 * 2 ** 30), len(order) - 1)
         if self.world_size > 1:                                  # all ranks must run the same kernel sequence
             t = torch.tensor([pick], device=self.device, dtype=torch.int32)
