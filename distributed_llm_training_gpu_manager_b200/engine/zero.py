@@ -250,7 +250,15 @@ class ZeroEngine:
         self.shard_params.copy_(self.master.to(dev, non_blocking=False).to(cd))
         # parameter / gradient buffers
         nblk = len(L.units) - 1
-        if self.stage >= 3 and nblk >= 2:
+        # One rank: nothing to gather or reduce — parameters and gradients *are* the shard buffers
+        # (per unit, the shard layout of replicated tensors equals the unit's full layout).
+        self._single = self.world_size == 1 and L.part_numel == 0
+        alias_grads = self._single and cfg.accum_dtype == cd
+        if self._single:
+            self._unit_pbuf = [self.shard_params[u.repl_shard_start:u.repl_shard_end] for u in L.units]
+            self._resident = [True] * len(L.units)
+            self._slot_owner = [None, None]
+        elif self.stage >= 3 and nblk >= 2:
             blk_numel = max(u.full_numel for u in L.units[1:])
             self._pbuf_root = torch.zeros(L.units[0].full_numel, dtype=cd, device=dev)
             self._pbuf_blk = [torch.zeros(blk_numel, dtype=cd, device=dev) for _ in range(2)]
@@ -266,9 +274,12 @@ class ZeroEngine:
                 off += u.full_numel
             self._resident = [True] * len(L.units)
             self._slot_owner = [None, None]
-        self.pooled_params = self.stage >= 3 and nblk >= 2
-        self.pooled_grads = self.stage >= 2 and nblk >= 2
-        if self.pooled_grads:
+        self.pooled_params = self.stage >= 3 and nblk >= 2 and not self._single
+        self.pooled_grads = self.stage >= 2 and nblk >= 2 and not alias_grads
+        self._grads_alias = alias_grads
+        if alias_grads:
+            self._unit_gbuf = [self.shard_grads[u.repl_shard_start:u.repl_shard_end] for u in L.units]
+        elif self.pooled_grads:
             blk_numel = max(u.full_numel for u in L.units[1:])
             self._gbuf_root = self._zeros(L.units[0].full_numel, cd, "gbuf_root", symmetric=True)
             self._gbuf_blk = [self._zeros(blk_numel, cd, f"gbuf_blk{i}", symmetric=True) for i in range(2)]
@@ -353,6 +364,8 @@ class ZeroEngine:
     # ------------------------------------------------------------------ stage-3 parameter residency
     def _gather_unit(self, ui: int, stream=None) -> None:
         """All-gather unit ``ui``'s rows into its buffer (X2). Replicated tensors are local copies."""
+        if self._single:
+            return                      # parameters are views of the shard: always current
         u = self.layout.units[ui]
         pb = self._unit_pbuf[ui]
         ctx = torch.cuda.stream(stream) if (stream is not None and self.on_cuda) else nullcontext()
@@ -402,6 +415,8 @@ class ZeroEngine:
         if self._reduced[ui]:
             return
         self._reduced[ui] = True
+        if self._grads_alias:
+            return                      # single rank: the unit's gradients already live in the shard
         u = self.layout.units[ui]
         gb = self._unit_gbuf[ui]
         use_side = self.on_cuda and self.cfg.overlap_comm
