@@ -28,7 +28,6 @@ from __future__ import annotations
 import re
 import subprocess
 import threading
-import time
 import xml.etree.ElementTree as ET
 from collections import deque
 from datetime import datetime, timezone

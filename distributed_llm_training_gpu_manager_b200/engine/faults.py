@@ -15,8 +15,6 @@ import signal
 from dataclasses import dataclass, field
 from typing import Optional, Set
 
-import torch
-
 
 @dataclass
 class FaultPlan:

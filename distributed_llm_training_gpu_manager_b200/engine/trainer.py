@@ -17,17 +17,15 @@ preemption, ``ai_engine/spot_resiliency.py``) finishes the current step, writes 
 from __future__ import annotations
 
 import json
-import os
 import signal
 import time
 from dataclasses import dataclass, field
-from typing import Any, Callable, Dict, Iterator, List, Optional, Tuple
+from typing import Any, Callable, Dict, List, Optional, Tuple
 
 import torch
 import torch.distributed as dist
 
-from ..ai_engine.loss_monitor import (AlertSeverity, HaltAction, HaltPolicy, LossSpikeMonitor, MonitorConfig,
-                                      SpikeAlert)
+from ..ai_engine.loss_monitor import AlertSeverity, HaltAction, HaltPolicy, LossSpikeMonitor, MonitorConfig
 from . import checkpoint as ckpt
 from .faults import FaultPlan
 

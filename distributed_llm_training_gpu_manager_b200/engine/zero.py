@@ -30,11 +30,10 @@ Design (see ``partition.py`` for the layout):
 """
 from __future__ import annotations
 
-import math
 import os
 import time
 from contextlib import contextmanager, nullcontext
-from typing import Any, Callable, Dict, Iterable, List, Optional, Tuple, Union
+from typing import Any, Callable, Dict, List, Optional, Tuple, Union
 
 import torch
 import torch.distributed as dist
@@ -42,7 +41,7 @@ import torch.nn as nn
 
 from ..ops import optim as O
 from .config import EngineConfig, load_config
-from .partition import Layout, ParamSpec, UnitLayout, build_layout
+from .partition import Layout, ParamSpec, build_layout
 from .schedules import DynamicLossScaler, LRSchedule
 
 _BLOCK_LIST_NAMES = ("blocks", "layers", "h", "transformer_blocks")
@@ -514,7 +513,8 @@ class ZeroEngine:
                 st[0] = self.fused.sumsq_part[0]
                 st[3] = self.fused.sumsq_repl[0]
             else:
-                O.sumsq(self.shard_grads[:L.part_numel], st[0:1], nonfinite_flag=self._flag) if L.part_numel else None
+                if L.part_numel:
+                    O.sumsq(self.shard_grads[:L.part_numel], st[0:1], nonfinite_flag=self._flag)
                 if L.shard_numel > L.part_numel:
                     O.sumsq(self.shard_grads[L.part_numel:], st[3:4], nonfinite_flag=self._flag)
             st[1] = self._flag.float()[0]

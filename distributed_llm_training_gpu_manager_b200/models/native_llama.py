@@ -19,7 +19,6 @@ The reference ships no model.
 """
 from __future__ import annotations
 
-import math
 from typing import Any, Dict, List, Optional, Tuple, Union
 
 import torch

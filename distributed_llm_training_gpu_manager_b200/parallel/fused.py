@@ -14,7 +14,6 @@ Division of labour per optimizer step (cf. ``engine/zero.py`` which does the sam
 """
 from __future__ import annotations
 
-import ctypes as C
 from typing import Dict, List, Optional
 
 import torch

@@ -4,7 +4,7 @@ avoids global-registry state between tests."""
 from __future__ import annotations
 
 import math
-from typing import Dict, Iterable
+from typing import Dict
 
 
 def _line(name: str, value: float, **labels: str) -> str:
