@@ -108,50 +108,62 @@ fused_reduce_scatter_kernel(const __grid_constant__ PeerTable pt, const Segment*
     const long long src0 = sg.full_off + (sg.partitioned ? (long long)rank * n : 0);
     const long long nvec = n >> 3;  // 8 bf16 per 128-bit load (layout guarantees 16-element alignment)
     float ss = 0.f;
-    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
-      float acc[8];
+    const long long vstride = (long long)gridDim.x * blockDim.x;
+    for (long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += 2 * vstride) {
+      // two vectors per iteration: 2*ws independent 128-bit peer loads in flight per thread
+      uint4 in[2][MAX_WS];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-      uint4 in[MAX_WS];
+      for (int u = 0; u < 2; ++u) {
+        const long long v = v0 + u * vstride;
+        if (v < nvec) {
 #pragma unroll
-      for (int p = 0; p < MAX_WS; ++p) {  // issue every peer load before consuming any (NVLink latency ~2 us)
-        if (p < ws) in[p] = ld_peer_v4(reinterpret_cast<const __nv_bfloat16*>(pt.data[p]) + src0 + v * 8);
-      }
-#pragma unroll
-      for (int p = 0; p < MAX_WS; ++p) {
-        if (p < ws) {
-          float2 t;
-          t = unpack_bf16x2(in[p].x); acc[0] += t.x; acc[1] += t.y;
-          t = unpack_bf16x2(in[p].y); acc[2] += t.x; acc[3] += t.y;
-          t = unpack_bf16x2(in[p].z); acc[4] += t.x; acc[5] += t.y;
-          t = unpack_bf16x2(in[p].w); acc[6] += t.x; acc[7] += t.y;
+          for (int p = 0; p < MAX_WS; ++p)
+            if (p < ws) in[u][p] = ld_peer_v4(reinterpret_cast<const __nv_bfloat16*>(pt.data[p]) + src0 + v * 8);
         }
       }
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] *= scale;
-      const long long d = sg.shard_off + v * 8;
-      if constexpr (ACC_F32) {
-        float* o = reinterpret_cast<float*>(shard_grads) + d;
-        float4 a = *reinterpret_cast<float4*>(o), b = *reinterpret_cast<float4*>(o + 4);
-        a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
-        b.x += acc[4]; b.y += acc[5]; b.z += acc[6]; b.w += acc[7];
-        *reinterpret_cast<float4*>(o) = a;
-        *reinterpret_cast<float4*>(o + 4) = b;
-        ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
-      } else {
-        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(shard_grads) + d;
-        const uint4 old = *reinterpret_cast<const uint4*>(o);
-        float2 t;
-        t = unpack_bf16x2(old.x); acc[0] += t.x; acc[1] += t.y;
-        t = unpack_bf16x2(old.y); acc[2] += t.x; acc[3] += t.y;
-        t = unpack_bf16x2(old.z); acc[4] += t.x; acc[5] += t.y;
-        t = unpack_bf16x2(old.w); acc[6] += t.x; acc[7] += t.y;
-        uint4 w;
-        w.x = pack_bf16x2(acc[0], acc[1]); w.y = pack_bf16x2(acc[2], acc[3]);
-        w.z = pack_bf16x2(acc[4], acc[5]); w.w = pack_bf16x2(acc[6], acc[7]);
-        *reinterpret_cast<uint4*>(o) = w;
+      for (int u = 0; u < 2; ++u) {
+        const long long v = v0 + u * vstride;
+        if (v >= nvec) continue;
+        float acc[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) ss += acc[e] * acc[e];
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+        for (int p = 0; p < MAX_WS; ++p) {   // fixed rank order: deterministic sums
+          if (p < ws) {
+            float2 t;
+            t = unpack_bf16x2(in[u][p].x); acc[0] += t.x; acc[1] += t.y;
+            t = unpack_bf16x2(in[u][p].y); acc[2] += t.x; acc[3] += t.y;
+            t = unpack_bf16x2(in[u][p].z); acc[4] += t.x; acc[5] += t.y;
+            t = unpack_bf16x2(in[u][p].w); acc[6] += t.x; acc[7] += t.y;
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] *= scale;
+        const long long d = sg.shard_off + v * 8;
+        if constexpr (ACC_F32) {
+          float* o = reinterpret_cast<float*>(shard_grads) + d;
+          float4 a = *reinterpret_cast<float4*>(o), b = *reinterpret_cast<float4*>(o + 4);
+          a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
+          b.x += acc[4]; b.y += acc[5]; b.z += acc[6]; b.w += acc[7];
+          *reinterpret_cast<float4*>(o) = a;
+          *reinterpret_cast<float4*>(o + 4) = b;
+          ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
+        } else {
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(shard_grads) + d;
+          const uint4 old = *reinterpret_cast<const uint4*>(o);
+          float2 t;
+          t = unpack_bf16x2(old.x); acc[0] += t.x; acc[1] += t.y;
+          t = unpack_bf16x2(old.y); acc[2] += t.x; acc[3] += t.y;
+          t = unpack_bf16x2(old.z); acc[4] += t.x; acc[5] += t.y;
+          t = unpack_bf16x2(old.w); acc[6] += t.x; acc[7] += t.y;
+          uint4 w;
+          w.x = pack_bf16x2(acc[0], acc[1]); w.y = pack_bf16x2(acc[2], acc[3]);
+          w.z = pack_bf16x2(acc[4], acc[5]); w.w = pack_bf16x2(acc[6], acc[7]);
+          *reinterpret_cast<uint4*>(o) = w;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) ss += acc[e] * acc[e];
+        }
       }
     }
     if (sg.partitioned) ss_part += ss; else ss_repl += ss;
@@ -316,7 +328,7 @@ pull_allgather_kernel(const __grid_constant__ PeerTable pt, const Segment* __res
     const long long nvec = n >> 3;
     const long long total = nvec * ws;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    constexpr int UNR = 4;  // four 128-bit peer loads in flight per thread
+    constexpr int UNR = 8;  // eight 128-bit peer loads in flight per thread (NVLink latency ~2 us)
     for (long long j0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; j0 < total; j0 += stride * UNR) {
       uint4 val[UNR];
 #pragma unroll
