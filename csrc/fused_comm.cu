@@ -108,62 +108,50 @@ fused_reduce_scatter_kernel(const __grid_constant__ PeerTable pt, const Segment*
     const long long src0 = sg.full_off + (sg.partitioned ? (long long)rank * n : 0);
     const long long nvec = n >> 3;  // 8 bf16 per 128-bit load (layout guarantees 16-element alignment)
     float ss = 0.f;
-    const long long vstride = (long long)gridDim.x * blockDim.x;
-    for (long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += 2 * vstride) {
-      // two vectors per iteration: 2*ws independent 128-bit peer loads in flight per thread
-      uint4 in[2][MAX_WS];
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
+      float acc[8];
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const long long v = v0 + u * vstride;
-        if (v < nvec) {
+      for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+      uint4 in[MAX_WS];
 #pragma unroll
-          for (int p = 0; p < MAX_WS; ++p)
-            if (p < ws) in[u][p] = ld_peer_v4(reinterpret_cast<const __nv_bfloat16*>(pt.data[p]) + src0 + v * 8);
+      for (int p = 0; p < MAX_WS; ++p) {  // issue every peer load before consuming any (NVLink latency ~2 us)
+        if (p < ws) in[p] = ld_peer_v4(reinterpret_cast<const __nv_bfloat16*>(pt.data[p]) + src0 + v * 8);
+      }
+#pragma unroll
+      for (int p = 0; p < MAX_WS; ++p) {
+        if (p < ws) {
+          float2 t;
+          t = unpack_bf16x2(in[p].x); acc[0] += t.x; acc[1] += t.y;
+          t = unpack_bf16x2(in[p].y); acc[2] += t.x; acc[3] += t.y;
+          t = unpack_bf16x2(in[p].z); acc[4] += t.x; acc[5] += t.y;
+          t = unpack_bf16x2(in[p].w); acc[6] += t.x; acc[7] += t.y;
         }
       }
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const long long v = v0 + u * vstride;
-        if (v >= nvec) continue;
-        float acc[8];
+      for (int e = 0; e < 8; ++e) acc[e] *= scale;
+      const long long d = sg.shard_off + v * 8;
+      if constexpr (ACC_F32) {
+        float* o = reinterpret_cast<float*>(shard_grads) + d;
+        float4 a = *reinterpret_cast<float4*>(o), b = *reinterpret_cast<float4*>(o + 4);
+        a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
+        b.x += acc[4]; b.y += acc[5]; b.z += acc[6]; b.w += acc[7];
+        *reinterpret_cast<float4*>(o) = a;
+        *reinterpret_cast<float4*>(o + 4) = b;
+        ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
+      } else {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(shard_grads) + d;
+        const uint4 old = *reinterpret_cast<const uint4*>(o);
+        float2 t;
+        t = unpack_bf16x2(old.x); acc[0] += t.x; acc[1] += t.y;
+        t = unpack_bf16x2(old.y); acc[2] += t.x; acc[3] += t.y;
+        t = unpack_bf16x2(old.z); acc[4] += t.x; acc[5] += t.y;
+        t = unpack_bf16x2(old.w); acc[6] += t.x; acc[7] += t.y;
+        uint4 w;
+        w.x = pack_bf16x2(acc[0], acc[1]); w.y = pack_bf16x2(acc[2], acc[3]);
+        w.z = pack_bf16x2(acc[4], acc[5]); w.w = pack_bf16x2(acc[6], acc[7]);
+        *reinterpret_cast<uint4*>(o) = w;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-#pragma unroll
-        for (int p = 0; p < MAX_WS; ++p) {   // fixed rank order: deterministic sums
-          if (p < ws) {
-            float2 t;
-            t = unpack_bf16x2(in[u][p].x); acc[0] += t.x; acc[1] += t.y;
-            t = unpack_bf16x2(in[u][p].y); acc[2] += t.x; acc[3] += t.y;
-            t = unpack_bf16x2(in[u][p].z); acc[4] += t.x; acc[5] += t.y;
-            t = unpack_bf16x2(in[u][p].w); acc[6] += t.x; acc[7] += t.y;
-          }
-        }
-#pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] *= scale;
-        const long long d = sg.shard_off + v * 8;
-        if constexpr (ACC_F32) {
-          float* o = reinterpret_cast<float*>(shard_grads) + d;
-          float4 a = *reinterpret_cast<float4*>(o), b = *reinterpret_cast<float4*>(o + 4);
-          a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
-          b.x += acc[4]; b.y += acc[5]; b.z += acc[6]; b.w += acc[7];
-          *reinterpret_cast<float4*>(o) = a;
-          *reinterpret_cast<float4*>(o + 4) = b;
-          ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
-        } else {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(shard_grads) + d;
-          const uint4 old = *reinterpret_cast<const uint4*>(o);
-          float2 t;
-          t = unpack_bf16x2(old.x); acc[0] += t.x; acc[1] += t.y;
-          t = unpack_bf16x2(old.y); acc[2] += t.x; acc[3] += t.y;
-          t = unpack_bf16x2(old.z); acc[4] += t.x; acc[5] += t.y;
-          t = unpack_bf16x2(old.w); acc[6] += t.x; acc[7] += t.y;
-          uint4 w;
-          w.x = pack_bf16x2(acc[0], acc[1]); w.y = pack_bf16x2(acc[2], acc[3]);
-          w.z = pack_bf16x2(acc[4], acc[5]); w.w = pack_bf16x2(acc[6], acc[7]);
-          *reinterpret_cast<uint4*>(o) = w;
-#pragma unroll
-          for (int e = 0; e < 8; ++e) ss += acc[e] * acc[e];
-        }
+        for (int e = 0; e < 8; ++e) ss += acc[e] * acc[e];
       }
     }
     if (sg.partitioned) ss_part += ss; else ss_repl += ss;
@@ -191,6 +179,145 @@ fused_reduce_scatter_kernel(const __grid_constant__ PeerTable pt, const Segment*
     }
   }
 }
+
+// -------------------------------------------------------------------------------------------------
+// K1, NVLS flavour (opt-in): the gradient buffer is additionally bound to an NVSwitch multicast object
+// (`mc` = multicast VA of pt.data[*]). Partitioned tensors are summed *inside the switch* by
+// multimem.ld_reduce — one 128-bit instruction returns the bf16 sum (fp32-accumulated) of the ws copies,
+// so this GPU receives 1/(ws-1) of the NVLink bytes and needs far fewer CTAs to keep the links busy.
+// Replicated tensors stay on the rank-ordered point-to-point path: every rank must produce the
+// bit-identical sum. A separate kernel so the default point-to-point kernel is untouched.
+// -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc_addr) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc_addr)
+               : "memory");
+  return v;
+}
+
+// shard[d .. d+8) += acc; returns the sum of squares of the new values
+template <bool ACC_F32>
+__device__ __forceinline__ float accumulate_shard(void* __restrict__ shard_grads, long long d, float (&acc)[8]) {
+  float ss = 0.f;
+  if constexpr (ACC_F32) {
+    float* o = reinterpret_cast<float*>(shard_grads) + d;
+    float4 a = *reinterpret_cast<float4*>(o), b = *reinterpret_cast<float4*>(o + 4);
+    a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
+    b.x += acc[4]; b.y += acc[5]; b.z += acc[6]; b.w += acc[7];
+    *reinterpret_cast<float4*>(o) = a;
+    *reinterpret_cast<float4*>(o + 4) = b;
+    ss = a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
+  } else {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(shard_grads) + d;
+    const uint4 old = *reinterpret_cast<const uint4*>(o);
+    float2 t;
+    t = unpack_bf16x2(old.x); acc[0] += t.x; acc[1] += t.y;
+    t = unpack_bf16x2(old.y); acc[2] += t.x; acc[3] += t.y;
+    t = unpack_bf16x2(old.z); acc[4] += t.x; acc[5] += t.y;
+    t = unpack_bf16x2(old.w); acc[6] += t.x; acc[7] += t.y;
+    uint4 w;
+    w.x = pack_bf16x2(acc[0], acc[1]); w.y = pack_bf16x2(acc[2], acc[3]);
+    w.z = pack_bf16x2(acc[4], acc[5]); w.w = pack_bf16x2(acc[6], acc[7]);
+    *reinterpret_cast<uint4*>(o) = w;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ss += acc[e] * acc[e];
+  }
+  return ss;
+}
+
+template <bool ACC_F32>
+__global__ void __launch_bounds__(COMM_THREADS)
+fused_reduce_scatter_nvls_kernel(const __grid_constant__ PeerTable pt, const void* __restrict__ mc_base,
+                                 const Segment* __restrict__ segs, int nseg, void* __restrict__ shard_grads, float scale,
+                                 float* __restrict__ sumsq_part, float* __restrict__ sumsq_repl,
+                                 int* __restrict__ nonfinite, unsigned int* block_counter, uint32_t epoch, int channel,
+                                 int rank, int ws, int use_barrier) {
+  __shared__ float red[32];
+  __shared__ int is_last;
+  if (use_barrier) signal_all_and_wait(pt, channel, 0, rank, ws, epoch, blockIdx.x == 0);
+
+  float ss_part = 0.f, ss_repl = 0.f;
+  const long long vstride = (long long)gridDim.x * blockDim.x;
+  for (int s = 0; s < nseg; ++s) {
+    const Segment sg = segs[s];
+    const long long n = sg.partitioned ? sg.numel / ws : sg.numel;
+    const long long src0 = sg.full_off + (sg.partitioned ? (long long)rank * n : 0);
+    const long long nvec = n >> 3;
+    float ss = 0.f;
+    if (sg.partitioned) {
+      // the round trip through the switch is longer than a peer load: keep NVLS_UNR requests in flight
+      constexpr int NVLS_UNR = 8;
+      const __nv_bfloat16* mc = reinterpret_cast<const __nv_bfloat16*>(mc_base) + src0;
+      for (long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += NVLS_UNR * vstride) {
+        uint4 in[NVLS_UNR];
+#pragma unroll
+        for (int u = 0; u < NVLS_UNR; ++u) {
+          const long long v = v0 + u * vstride;
+          if (v < nvec) in[u] = multimem_ld_reduce_bf16x8(mc + v * 8);
+        }
+#pragma unroll
+        for (int u = 0; u < NVLS_UNR; ++u) {
+          const long long v = v0 + u * vstride;
+          if (v >= nvec) continue;
+          float acc[8];
+          float2 t;
+          t = unpack_bf16x2(in[u].x); acc[0] = t.x * scale; acc[1] = t.y * scale;
+          t = unpack_bf16x2(in[u].y); acc[2] = t.x * scale; acc[3] = t.y * scale;
+          t = unpack_bf16x2(in[u].z); acc[4] = t.x * scale; acc[5] = t.y * scale;
+          t = unpack_bf16x2(in[u].w); acc[6] = t.x * scale; acc[7] = t.y * scale;
+          ss += accumulate_shard<ACC_F32>(shard_grads, sg.shard_off + v * 8, acc);
+        }
+      }
+      ss_part += ss;
+    } else {
+      for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += vstride) {
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+        uint4 in[MAX_WS];
+#pragma unroll
+        for (int p = 0; p < MAX_WS; ++p)
+          if (p < ws) in[p] = ld_peer_v4(reinterpret_cast<const __nv_bfloat16*>(pt.data[p]) + src0 + v * 8);
+#pragma unroll
+        for (int p = 0; p < MAX_WS; ++p) {   // fixed rank order: deterministic, identical on every rank
+          if (p < ws) {
+            float2 t;
+            t = unpack_bf16x2(in[p].x); acc[0] += t.x; acc[1] += t.y;
+            t = unpack_bf16x2(in[p].y); acc[2] += t.x; acc[3] += t.y;
+            t = unpack_bf16x2(in[p].z); acc[4] += t.x; acc[5] += t.y;
+            t = unpack_bf16x2(in[p].w); acc[6] += t.x; acc[7] += t.y;
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] *= scale;
+        ss += accumulate_shard<ACC_F32>(shard_grads, sg.shard_off + v * 8, acc);
+      }
+      ss_repl += ss;
+    }
+  }
+  const float tp = block_sum(ss_part, red);
+  const float tr = block_sum(ss_repl, red);
+  if (threadIdx.x == 0) {
+    sumsq_part[blockIdx.x] = tp;
+    sumsq_repl[blockIdx.x] = tr;
+    if (!(isfinite(tp) && isfinite(tr)) && nonfinite != nullptr) atomicOr(nonfinite, 1);
+  }
+  if (use_barrier) {   // phase 1, as in the point-to-point kernel
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      is_last = (atomicAdd(block_counter, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+      if (threadIdx.x == 0) *block_counter = 0;
+      signal_all_and_wait(pt, channel, 1, rank, ws, epoch, true);
+    }
+  }
+}
+
 
 __global__ void fold_partials_kernel(const float* __restrict__ part, int P, float* __restrict__ out_part,
                                      float* __restrict__ out_repl, int accumulate) {
@@ -328,7 +455,7 @@ pull_allgather_kernel(const __grid_constant__ PeerTable pt, const Segment* __res
     const long long nvec = n >> 3;
     const long long total = nvec * ws;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    constexpr int UNR = 8;  // eight 128-bit peer loads in flight per thread (NVLink latency ~2 us)
+    constexpr int UNR = 4;  // four 128-bit peer loads in flight per thread
     for (long long j0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; j0 < total; j0 += stride * UNR) {
       uint4 val[UNR];
 #pragma unroll
@@ -369,6 +496,8 @@ static void comm_kernels_setup_once() {
   if (done) return;
   prefer_max_shared_carveout(fused_reduce_scatter_kernel<true>);
   prefer_max_shared_carveout(fused_reduce_scatter_kernel<false>);
+  prefer_max_shared_carveout(fused_reduce_scatter_nvls_kernel<true>);
+  prefer_max_shared_carveout(fused_reduce_scatter_nvls_kernel<false>);
   prefer_max_shared_carveout(fused_adam_push_kernel<true>);
   prefer_max_shared_carveout(fused_adam_push_kernel<false>);
   prefer_max_shared_carveout(pull_allgather_kernel);
@@ -459,6 +588,34 @@ int bz_fused_reduce_scatter(void* const* grad_ptrs, void* const* signal_ptrs, co
     fused_reduce_scatter_kernel<false><<<ctas, COMM_THREADS, 0, st>>>(pt, (const Segment*)segs, nseg, shard_grads, scale,
                                                                       workspace, workspace + ctas, nonfinite_flag, counter,
                                                                       epoch, channel, rank, ws, use_barrier);
+  BZ_CUDA_CHECK(cudaGetLastError());
+  fold_partials_kernel<<<1, 256, 0, st>>>(workspace, ctas, sumsq_part, sumsq_repl, 1);
+  BZ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// NVLS variant (opt-in): grad_mc is the multicast mapping of the same gradient buffer on all ranks.
+int bz_fused_reduce_scatter_mc(void* const* grad_ptrs, void* const* signal_ptrs, void* grad_mc, const void* segs,
+                               int nseg, void* shard_grads, int shard_is_f32, float scale, float* workspace,
+                               float* sumsq_part, float* sumsq_repl, int* nonfinite_flag, unsigned int epoch,
+                               int channel, int rank, int ws, int use_barrier, int ctas, void* stream) {
+  PeerTable pt;
+  if (int rc = fill_table(pt, grad_ptrs, signal_ptrs, ws)) return rc;
+  BZ_REQUIRE(grad_mc != nullptr, "fused_reduce_scatter_mc: null multicast pointer");
+  BZ_REQUIRE(channel >= 0 && channel < SIG_CHANNELS, "fused_reduce_scatter_mc: channel %d out of range", channel);
+  BZ_REQUIRE(!use_barrier || signal_ptrs != nullptr, "fused_reduce_scatter_mc: barrier requested without signal pads");
+  if (ctas <= 0) ctas = 32;
+  if (ctas > 1024) ctas = 1024;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned int* counter = reinterpret_cast<unsigned int*>(workspace + 2 * 1024);
+  if (shard_is_f32)
+    fused_reduce_scatter_nvls_kernel<true><<<ctas, COMM_THREADS, 0, st>>>(
+        pt, grad_mc, (const Segment*)segs, nseg, shard_grads, scale, workspace, workspace + ctas, nonfinite_flag,
+        counter, epoch, channel, rank, ws, use_barrier);
+  else
+    fused_reduce_scatter_nvls_kernel<false><<<ctas, COMM_THREADS, 0, st>>>(
+        pt, grad_mc, (const Segment*)segs, nseg, shard_grads, scale, workspace, workspace + ctas, nonfinite_flag,
+        counter, epoch, channel, rank, ws, use_barrier);
   BZ_CUDA_CHECK(cudaGetLastError());
   fold_partials_kernel<<<1, 256, 0, st>>>(workspace, ctas, sumsq_part, sumsq_repl, 1);
   BZ_CUDA_CHECK(cudaGetLastError());

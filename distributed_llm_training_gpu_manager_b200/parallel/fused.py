@@ -19,7 +19,7 @@ from typing import Dict, List, Optional
 import torch
 
 from ..ops import lib as _lib
-from .symm import SymmetricBuffer
+from .symm import SymmetricBuffer, nvls_buffer_or_none
 
 RS_CHANNEL, ADAM_CHANNEL = 0, 1
 
@@ -36,6 +36,7 @@ class FusedComm:
         import os
         rs_ctas = rs_ctas or int(os.environ.get("B200ZERO_RS_CTAS", "128"))
         adam_ctas = adam_ctas or int(os.environ.get("B200ZERO_ADAM_CTAS", "148"))
+        self.nvls_ctas = int(os.environ.get("B200ZERO_NVLS_CTAS", "32"))
         self.use_fused_gather = os.environ.get("B200ZERO_FUSED_GATHER", "1") == "1"
         self.use_fused_rs = os.environ.get("B200ZERO_FUSED_RS", "1") == "1"
         assert engine.on_cuda, "fused communication needs GPUs"
@@ -58,12 +59,20 @@ class FusedComm:
             self._unit_segs[u.index] = segment_table(
                 [(s.full_offset, s.numel, s.shard_offset, s.partitioned) for s in u.params], dev)
         self.launches = 0
+        self.nvls_launches = 0
 
     # -- symmetric buffers are created by the engine through this hook --------------------------------
     @staticmethod
     def alloc(engine, numel: int, dtype: torch.dtype, name: str) -> torch.Tensor:
+        import os
         es = torch.empty((), dtype=dtype).element_size()
-        buf = SymmetricBuffer(numel * es, device=engine.device)
+        buf = None
+        # NVLS (opt-in, experimental): gradient buffers additionally bound to an NVSwitch multicast object so
+        # K1 reduces inside the switch. Everything else stays on the plain IPC mapping.
+        if os.environ.get("B200ZERO_NVLS", "0") == "1" and name.startswith("gbuf"):
+            buf = nvls_buffer_or_none(numel * es, engine.device)
+        if buf is None:
+            buf = SymmetricBuffer(numel * es, device=engine.device)
         engine._symm[name] = buf
         return buf.tensor(dtype, numel)
 
@@ -74,6 +83,15 @@ class FusedComm:
             if buf.local_ptr <= p < buf.local_ptr + buf.nbytes:
                 return buf.ptr_array(p - buf.local_ptr)
         raise RuntimeError("tensor is not in symmetric memory")
+
+    def _mc_for(self, tensor: torch.Tensor) -> int:
+        """Multicast address of the same bytes (0 when the buffer has no NVLS mapping)."""
+        p = tensor.data_ptr()
+        for buf in self.e._symm.values():
+            if buf.local_ptr <= p < buf.local_ptr + buf.nbytes:
+                mc = getattr(buf, "multicast_ptr", 0)
+                return mc + (p - buf.local_ptr) if mc else 0
+        return 0
 
     # -- K1 ------------------------------------------------------------------------------------
     def begin_micro_step(self) -> None:
@@ -86,11 +104,17 @@ class FusedComm:
             return False
         gb = e._unit_gbuf[ui]
         self.epoch[RS_CHANNEL] += 1
-        rc = self.L.bz_fused_reduce_scatter(
-            self._ptrs_for(gb), self._sig_ptrs, self._unit_segs[ui].data_ptr(), len(e.layout.units[ui].params),
-            e.shard_grads.data_ptr(), int(e.shard_grads.dtype == torch.float32), scale, self.workspace.data_ptr(),
-            self.sumsq_part.data_ptr(), self.sumsq_repl.data_ptr(), e._flag.data_ptr(), self.epoch[RS_CHANNEL],
-            RS_CHANNEL, e.rank, e.world_size, 1, self.rs_ctas, _lib.stream())
+        tail = (self._unit_segs[ui].data_ptr(), len(e.layout.units[ui].params),
+                e.shard_grads.data_ptr(), int(e.shard_grads.dtype == torch.float32), scale, self.workspace.data_ptr(),
+                self.sumsq_part.data_ptr(), self.sumsq_repl.data_ptr(), e._flag.data_ptr(), self.epoch[RS_CHANNEL],
+                RS_CHANNEL, e.rank, e.world_size, 1, self.rs_ctas, _lib.stream())
+        mc = self._mc_for(gb)
+        if mc:
+            tail = tail[:-2] + (self.nvls_ctas, tail[-1])      # the switch does the summing: fewer CTAs suffice
+            rc = self.L.bz_fused_reduce_scatter_mc(self._ptrs_for(gb), self._sig_ptrs, mc, *tail)
+            self.nvls_launches += 1
+        else:
+            rc = self.L.bz_fused_reduce_scatter(self._ptrs_for(gb), self._sig_ptrs, *tail)
         _lib.check(rc, "fused_reduce_scatter")
         _lib.add_launches(1)
         return True
@@ -125,12 +149,12 @@ class FusedComm:
                 recs = [(0, s.numel, s.shard_offset, s.partitioned) for u in e.layout.units for s in u.params]
                 self._all_segs = segment_table(recs, e.device)
             segs, nseg, pptrs = self._all_segs, self._all_segs.shape[0], None
-        rc = self.L.bz_fused_adam_push(
-            pptrs, self._sig_ptrs, segs.data_ptr(), nseg, e.master.data_ptr(), e.exp_avg.data_ptr(),
-            e.exp_avg_sq.data_ptr(), e.shard_grads.data_ptr(), int(e.shard_grads.dtype == torch.float32),
-            e.shard_params.data_ptr(), lr, cfg.betas[0], cfg.betas[1], cfg.eps, cfg.weight_decay, step_no,
-            e._coef.data_ptr(), e._flag.data_ptr(), self.workspace.data_ptr(), self.epoch[ADAM_CHANNEL], ADAM_CHANNEL,
-            e.rank, e.world_size, push, 1, 1, self.adam_ctas, _lib.stream())
+        tail = (segs.data_ptr(), nseg, e.master.data_ptr(), e.exp_avg.data_ptr(),
+                e.exp_avg_sq.data_ptr(), e.shard_grads.data_ptr(), int(e.shard_grads.dtype == torch.float32),
+                e.shard_params.data_ptr(), lr, cfg.betas[0], cfg.betas[1], cfg.eps, cfg.weight_decay, step_no,
+                e._coef.data_ptr(), e._flag.data_ptr(), self.workspace.data_ptr(), self.epoch[ADAM_CHANNEL],
+                ADAM_CHANNEL, e.rank, e.world_size, push, 1, 1, self.adam_ctas, _lib.stream())
+        rc = self.L.bz_fused_adam_push(pptrs, self._sig_ptrs, *tail)
         _lib.check(rc, "fused_adam_push")
 
     def close(self) -> None:

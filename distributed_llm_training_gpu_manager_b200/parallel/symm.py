@@ -92,3 +92,65 @@ class SymmetricBuffer:
 def _check(L, rc: int, what: str) -> None:
     if rc != 0:
         raise RuntimeError(f"b200zero {what} failed (rc={rc}): {L.bz_last_error().decode(errors='replace')}")
+
+
+class TorchSymmetricBuffer:
+    """Same interface as :class:`SymmetricBuffer`, but allocated and rendezvoused through
+    ``torch.distributed._symmetric_memory`` (CUDA VMM + fabric/fd handle exchange), which also binds
+    the allocation into an NVLS multicast object when the fabric supports it. Only allocation and
+    address exchange are borrowed; every kernel that touches the memory is ours. ``multicast_ptr`` is
+    0 when NVLS is unavailable."""
+
+    def __init__(self, nbytes: int, group=None, device: Optional[torch.device] = None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.nbytes = int((nbytes + 255) // 256 * 256)
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self.world = dist.get_world_size(self.group)
+        self._bytes = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+        self._hdl = symm_mem.rendezvous(self._bytes, self.group)
+        self._bytes.zero_()
+        self.peer_ptrs: List[int] = [int(p) for p in self._hdl.buffer_ptrs]
+        self.local_ptr = self.peer_ptrs[self.rank]
+        try:
+            self.multicast_ptr = int(self._hdl.multicast_ptr or 0)
+        except Exception:
+            self.multicast_ptr = 0
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+
+    def tensor(self, dtype: torch.dtype, numel: Optional[int] = None, byte_offset: int = 0) -> torch.Tensor:
+        es = torch.empty((), dtype=dtype).element_size()
+        if numel is None:
+            numel = (self.nbytes - byte_offset) // es
+        return self._bytes[byte_offset:byte_offset + numel * es].view(dtype)
+
+    def ptr_array(self, byte_offset: int = 0):
+        arr = (C.c_void_p * self.world)()
+        for r in range(self.world):
+            arr[r] = self.peer_ptrs[r] + byte_offset
+        return arr
+
+    def close(self) -> None:
+        self._hdl = None
+        self._bytes = None
+
+
+def nvls_buffer_or_none(nbytes: int, device: torch.device):
+    """A multicast-capable symmetric buffer, or None when NVLS cannot be used (collective call: every
+    rank gets the same answer)."""
+    ok, buf = 1, None
+    try:
+        buf = TorchSymmetricBuffer(nbytes, device=device)
+        if not buf.multicast_ptr:
+            ok = 0
+    except Exception:
+        ok = 0
+    t = torch.tensor([ok], device=device, dtype=torch.int32)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if not bool(t.item()):
+        if buf is not None:
+            buf.close()
+        return None
+    return buf

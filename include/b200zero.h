@@ -154,6 +154,15 @@ int bz_fused_adam_push(void* const* param_ptrs, void* const* signal_ptrs, const 
                        int channel, int rank, int ws, int push, int use_barrier, int zero_grads, int ctas,
                        void* stream);
 
+/* ---- K1, NVLS flavour (opt-in): the gradient buffer is additionally mapped through an NVSwitch
+ * multicast object (grad_mc = multicast VA of the buffer whose per-rank VAs are in grad_ptrs).
+ * Partitioned tensors are summed inside the switch (multimem.ld_reduce); replicated tensors,
+ * barriers and outputs are exactly as in bz_fused_reduce_scatter. */
+int bz_fused_reduce_scatter_mc(void* const* grad_ptrs, void* const* signal_ptrs, void* grad_mc, const void* segs,
+                               int nseg, void* shard_grads, int shard_is_f32, float scale, float* workspace,
+                               float* sumsq_part, float* sumsq_repl, int* nonfinite_flag, unsigned int epoch,
+                               int channel, int rank, int ws, int use_barrier, int ctas, void* stream);
+
 /* ---- pull all-gather of a unit's rows from every peer's shard (ZeRO-3, X2) ---------- */
 int bz_pull_allgather(void* const* shard_param_ptrs, const void* segs, int nseg, void* dst_unit, int rank, int ws,
                       int ctas, void* stream);

@@ -19,7 +19,7 @@ sys.path.insert(0, str(ROOT))
 from distributed_llm_training_gpu_manager_b200.ops import gemm as G, lib as bz  # noqa: E402
 from distributed_llm_training_gpu_manager_b200.ops.ag_gemm import ag_linear_fwd  # noqa: E402
 from distributed_llm_training_gpu_manager_b200.parallel.fused import segment_table  # noqa: E402
-from distributed_llm_training_gpu_manager_b200.parallel.symm import SymmetricBuffer  # noqa: E402
+from distributed_llm_training_gpu_manager_b200.parallel.symm import SymmetricBuffer, nvls_buffer_or_none  # noqa: E402
 
 NVLINK_GBS = 770.0
 
@@ -115,6 +115,21 @@ def main():
     res["K1_fused_reduce_scatter"] = {"ms": ms, "nvlink_bytes_in": remote, "achieved_gbs": remote / ms / 1e6,
                                       "target_ms": target, "fraction_of_roofline": target / ms,
                                       "nccl_rs_plus_scale_norm_ms": ms_nccl}
+    # K1 with the in-switch reduction (NVLS multimem.ld_reduce), when the fabric has multicast
+    nv = nvls_buffer_or_none(n * 2, dev) if os.environ.get("B200ZERO_BENCH_NVLS", "0") == "1" else None
+    if nv is not None:
+        nv.tensor(torch.bfloat16, n).copy_(g)
+        torch.cuda.synchronize(); dist.barrier()
+        for ctas in (32, 64, 128):
+            def k1mc():
+                epoch[0] += 1
+                bz.check(L.bz_fused_reduce_scatter_mc(nv.ptr_array(), sig.ptr_array(), nv.multicast_ptr, segs.data_ptr(),
+                                                      1, shard_g.data_ptr(), 0, 1.0 / ws, wsb.data_ptr(), sp.data_ptr(),
+                                                      sr.data_ptr(), flag.data_ptr(), epoch[0], 0, rank, ws, 1, ctas,
+                                                      bz.stream()), "rs_mc")
+            ms = timeit(k1mc)
+            res[f"K1_nvls_ctas{ctas}"] = {"ms": ms, "effective_gbs": remote / ms / 1e6,
+                                          "vs_p2p": res["K1_fused_reduce_scatter"]["ms"] / ms}
     # K3: AdamW + push all-gather
     pbuf = SymmetricBuffer(n * 2, device=dev)
     master = torch.randn(n // ws, device=dev); m_ = torch.zeros_like(master); v_ = torch.zeros_like(master)
@@ -134,6 +149,8 @@ def main():
     target = max(out_bytes / (NVLINK_GBS * 1e9), hbm_bytes / hbm) * 1e3
     res["K3_fused_adam_push"] = {"ms": ms, "nvlink_bytes_out": out_bytes, "achieved_gbs": out_bytes / ms / 1e6,
                                  "target_ms": target, "fraction_of_roofline": target / ms}
+    if nv is not None:
+        nv.close()
     # pull all-gather (ZeRO-3 bulk gather used in backward)
     sbuf = SymmetricBuffer((n // ws) * 2, device=dev)
     sbuf.tensor(torch.bfloat16, n // ws).copy_(torch.randn(n // ws, device=dev).bfloat16())

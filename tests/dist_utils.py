@@ -65,7 +65,7 @@ def _entry_nccl(rank, world, port, fn, args, ret):
             dist.destroy_process_group()
 
 
-def run_ranks_nccl(fn, world: int, args=()):
+def run_ranks_nccl(fn, world: int, args=(), timeout: float = 900):
     """One process per GPU over NCCL on this node."""
     ctx = mp.get_context("spawn")
     with ctx.Manager() as mgr:
@@ -75,7 +75,7 @@ def run_ranks_nccl(fn, world: int, args=()):
         for p in procs:
             p.start()
         for p in procs:
-            p.join(900)
+            p.join(timeout)
         for p in procs:
             if p.is_alive():
                 p.kill()

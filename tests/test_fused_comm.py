@@ -135,8 +135,10 @@ def test_adam_push_and_pull_allgather_emulated():
             assert torch.equal(dst[fo:fo + n], params[r][fo:fo + n]) or not part
 
 
-def _fused_vs_nccl_rank(rank, world, stage, gas=1):
+def _fused_vs_nccl_rank(rank, world, stage, gas=1, nvls=False):
+    import os
     import torch.distributed as dist
+    os.environ["B200ZERO_NVLS"] = "1" if nvls else "0"
     from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
     from distributed_llm_training_gpu_manager_b200.models import get_config
     from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
@@ -160,8 +162,30 @@ def _fused_vs_nccl_rank(rank, world, stage, gas=1):
         out[comm] = ([m["loss"] for m in ms], [m["grad_norm"] for m in ms],
                      eng.full_param("blocks.0.wqkv.weight").float().cpu())
         if eng.fused is not None:
+            out["nvls_launches"] = eng.fused.nvls_launches
             torch.cuda.synchronize(); dist.barrier(); eng.fused.close()
     return out
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("stage", [2, 3])
+def test_nvls_multimem_path_matches_nccl(stage):
+    """B200ZERO_NVLS=1: K1 reduces in the NVSwitch (multimem.ld_reduce).
+    Opt-in (B200ZERO_TEST_NVLS=1): the default product path is point-to-point; skipped (not failed) where
+    the fabric exposes no multicast object."""
+    import os
+    if os.environ.get("B200ZERO_TEST_NVLS", "0") != "1":
+        pytest.skip("NVLS path is opt-in: set B200ZERO_TEST_NVLS=1")
+    from dist_utils import run_ranks_nccl
+    world = min(torch.cuda.device_count(), 4)
+    outs = run_ranks_nccl(_fused_vs_nccl_rank, world, (stage, 1, True), timeout=240)
+    if all(o.get("nvls_launches", 0) == 0 for o in outs):
+        pytest.skip("no NVLS multicast support on this box")
+    for out in outs:
+        assert out["nvls_launches"] > 0
+        assert out["fused"][0] == pytest.approx(out["nccl"][0], rel=2e-3)
+        assert out["fused"][1] == pytest.approx(out["nccl"][1], rel=2e-2)
+        assert torch.allclose(out["fused"][2], out["nccl"][2], rtol=2e-2, atol=2e-3)
 
 
 @pytest.mark.multigpu
