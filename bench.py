@@ -47,10 +47,62 @@ def parse_args():
     ap.add_argument("--engine", default="auto", help="auto | native | module (generic nn.Module ZeRO engine)")
     ap.add_argument("--attn", default=None, help="attention backend override: native | sdpa")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--skip-halt", action="store_true", help="skip the spike-to-halt measurement after the timed regions")
     ap.add_argument("--breakdown", action="store_true", help="after the timed region, run one extra step with per-phase CUDA-event timers")
     ap.add_argument("--torch-profile", default=None, help="write a per-kernel CUDA-time table of one extra step to this file (rank 0)")
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model (result is not a bench value)")
     return ap.parse_args()
+
+
+# --------------------------------------------------------------------------- spike-to-halt (second half of the metric)
+def measure_spike_to_halt(engine, batch, history, steps_needed=10):
+    """Inject (a) a NaN gradient and (b) a x50 loss spike into one optimizer step each — through the
+    same FaultPlan hooks the recovery drills use — and time how long it takes until the training loop
+    holds a halt/rollback decision from LossSpikeMonitor + HaltPolicy. Clocks start when the offending
+    backward pass has finished on the device (the first moment the fault is observable in gradient
+    memory); ``from_forward_end`` additionally counts that backward pass (the loss value exists as soon
+    as the forward ends, but the engine reads it with the step's other by-products to avoid a mid-step
+    sync). Not part of any timed throughput region. Returns milliseconds on this rank."""
+    import torch
+    from distributed_llm_training_gpu_manager_b200.ai_engine.loss_monitor import HaltPolicy, LossSpikeMonitor
+    from distributed_llm_training_gpu_manager_b200.engine.faults import FaultPlan
+
+    mon, policy = LossSpikeMonitor(), HaltPolicy()
+    ids, lab = batch
+    while len(history) < steps_needed:              # the spike detector needs a 10-step window
+        engine.backward(engine(ids, lab))
+        history.append(engine.step()["loss"])
+    for i, loss in enumerate(history):
+        mon.ingest_device_flags(step=i + 1, loss=loss, nonfinite_grads=False, grad_norm_sq=1.0, learning_rate=0.0)
+    base = len(history)
+    res = {}
+    def _sync():
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+
+    for k, name in enumerate(("nan_grad", "loss_spike_x50")):
+        nxt = engine.global_steps + 1
+        plan = FaultPlan(nan_grad_at=nxt) if name == "nan_grad" else FaultPlan(spike_at=nxt, spike_factor=50.0)
+        plan.install(engine)
+        try:
+            _sync()
+            loss = engine(ids, lab)
+            _sync()
+            t_fwd = time.perf_counter()
+            engine.backward(loss)
+            _sync()
+            t_bwd = time.perf_counter()
+            m = engine.step()
+            alerts = mon.ingest_device_flags(step=base + k + 1, loss=m["loss"], nonfinite_grads=bool(m["nonfinite"]),
+                                             grad_norm_sq=m["grad_norm_sq"], learning_rate=m["lr"])
+            action = policy.decide(alerts, 0)
+            t_dec = time.perf_counter()
+        finally:
+            engine.fault_hooks.pop("pre_backward", None)
+            engine.fault_hooks.pop("post_backward", None)
+        res[name] = {"from_backward_end": (t_dec - t_bwd) * 1e3, "from_forward_end": (t_dec - t_fwd) * 1e3,
+                     "action": action.value, "alerts": [a.alert_type + "/" + a.severity.value for a in alerts]}
+    return res
 
 
 # --------------------------------------------------------------------------- reference arm
@@ -203,8 +255,9 @@ def run_ours(args) -> int:
         torch.cuda.synchronize()
 
     # ---- warm-up ----
+    loss_hist = []
     for i in range(args.warmup):
-        engine.train_step(*dev[i % n_pool])
+        loss_hist.append(engine.train_step(*dev[i % n_pool])["loss"])
     sync_all()
 
     # ---- device-timed region: exactly K steps ----
@@ -218,6 +271,7 @@ def run_ours(args) -> int:
     last = None
     for i in range(args.steps):
         last = engine.train_step(*dev[i % n_pool])
+        loss_hist.append(last["loss"])               # already a host float (step() reads the stats vector)
     e1.record()
     sync_all()
     torch.cuda.profiler.stop()
@@ -236,7 +290,7 @@ def run_ours(args) -> int:
             ids = host[i % n_pool][0].to(device, non_blocking=True)
             lab = host[i % n_pool][1].to(device, non_blocking=True)
             m = engine.train_step(ids, lab)
-            _ = float(m["loss"])
+            loss_hist.append(float(m["loss"]))
         sync_all()
         e2e_ms = (time.perf_counter() - t0) * 1e3
 
@@ -262,11 +316,32 @@ def run_ours(args) -> int:
             with open(args.torch_profile, "w") as f:
                 f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))
 
+    # ---- spike-to-halt: after every timed region; a failure here never costs the throughput line ----
+    halt = None
+    if not args.skip_halt:
+        try:
+            sync_all()
+            halt = measure_spike_to_halt(engine, dev[0], [x for x in loss_hist if x == x])
+        except Exception as exc:  # noqa: BLE001
+            halt = {"error": f"{type(exc).__name__}: {exc}"}
+    halt_ms = [0.0, 0.0, 0.0]
+    if halt and "error" not in halt:
+        halt_ms = [halt["nan_grad"]["from_backward_end"], halt["loss_spike_x50"]["from_backward_end"],
+                   halt["loss_spike_x50"]["from_forward_end"]]
+
     # ---- max over ranks ----
-    t = torch.tensor([ms_total, e2e_ms or 0.0], device=device, dtype=torch.float64)
+    t = torch.tensor([ms_total, e2e_ms or 0.0] + halt_ms, device=device, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, e2e_total = float(t[0]), float(t[1])
+    if halt and "error" not in halt:
+        halt = {"nan_grad_ms": round(float(t[2]), 3), "loss_spike_x50_ms": round(float(t[3]), 3),
+                "loss_spike_x50_from_forward_end_ms": round(float(t[4]), 2),
+                "actions": {"nan_grad": halt["nan_grad"]["action"], "loss_spike_x50": halt["loss_spike_x50"]["action"]},
+                "alerts": {"nan_grad": halt["nan_grad"]["alerts"], "loss_spike_x50": halt["loss_spike_x50"]["alerts"]},
+                "definition": "max over ranks; device-synchronised end of the offending backward pass -> halt/rollback "
+                              "decision in hand (stats all-reduce + pinned D2H + LossSpikeMonitor + HaltPolicy); the "
+                              "parameter update of a non-finite step is skipped on the device inside that same step"}
     tokens_per_step = MB * S * world
     value = tokens_per_step * args.steps / (ms_total / 1e3)
     flops_tok = mcfg.flops_per_token(S, recompute=False)      # model FLOPs (6·N + attention): recompute not counted
@@ -294,6 +369,8 @@ def run_ours(args) -> int:
         "final_loss": last["loss"] if last else None,
         "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 1),
     }
+    if halt is not None:
+        out["spike_to_halt_ms"] = halt
     if breakdown is not None:
         out["breakdown_ms"] = {k: round(v, 2) for k, v in breakdown.items()}
     if e2e_ms is not None:
