@@ -376,8 +376,11 @@ class DeepSpeedLauncher:
             notes.append("both bf16 and fp16 requested; bf16 takes precedence")
         if config.bf16_enabled and config.communication_data_type == "fp16":
             notes.append("communication_data_type 'fp16' with bf16 compute: the native engine reduces in bf16/fp32")
-        if OffloadDevice.NVME in (config.offload_optimizer, config.offload_param):
-            notes.append("nvme offload is accepted in the schema but served from pinned host memory by the native engine")
+        if config.offload_optimizer is OffloadDevice.NVME:
+            notes.append("offload_optimizer=nvme: state files go to offload_optimizer.nvme_path, else $B200ZERO_NVME_PATH, "
+                         "else <tmp>/b200zero_nvme (the reference schema has no nvme_path field)")
+        if config.offload_param is OffloadDevice.NVME:
+            notes.append("offload_param=nvme is accepted in the schema; parameters are kept sharded in HBM by the native engine")
         if config.elastic_training and config.num_nodes > 1:
             notes.append("elasticity.max_train_batch_size ignores num_nodes (reference behaviour kept)")
         return notes

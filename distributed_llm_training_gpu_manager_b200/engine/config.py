@@ -34,6 +34,8 @@ class EngineConfig:
     offload_optimizer: str = "none"
     offload_param: str = "none"
     pin_memory: bool = True
+    nvme_path: Optional[str] = None       # offload_optimizer.nvme_path (DeepSpeed key); default $B200ZERO_NVME_PATH or tmp
+    offload_buffer_count: int = 4         # offload_optimizer.buffer_count: staging slots of the NVMe tier
     # precision
     precision: str = "fp32"  # fp32 | fp16 | bf16
     loss_scale: float = 0.0
@@ -122,6 +124,8 @@ def load_config(src: Union[str, Dict[str, Any], EngineConfig]) -> EngineConfig:
     c.offload_optimizer = oo.get("device", "none") if c.stage >= 1 else "none"
     c.offload_param = op.get("device", "none") if c.stage >= 3 else "none"
     c.pin_memory = bool(oo.get("pin_memory", True))
+    c.nvme_path = oo.get("nvme_path")
+    c.offload_buffer_count = int(oo.get("buffer_count", 4))
     if (d.get("bf16") or {}).get("enabled"):
         c.precision = "bf16"
     elif (d.get("fp16") or {}).get("enabled"):

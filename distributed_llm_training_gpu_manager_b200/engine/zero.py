@@ -150,6 +150,7 @@ class ZeroEngine:
         # when peers cannot be mapped (no P2P/IPC) or the dtype is not bf16
         self._want_fused = (comm in ("fused", "auto") and self.on_cuda and self.world_size > 1
                             and self.cfg.compute_dtype == torch.bfloat16
+                            and self.cfg.offload_optimizer == "none"     # K3 updates device-resident state
                             and os.environ.get("B200ZERO_COMM", comm) != "nccl")
         if self._want_fused and comm == "auto":
             self._want_fused = self._probe_peer_memory()
@@ -231,8 +232,19 @@ class ZeroEngine:
         L, cfg, dev, cd = self.layout, self.cfg, self.device, self.compute_dtype
         state_dev = torch.device("cpu") if cfg.offload_optimizer in ("cpu", "nvme") else dev
         pin = state_dev.type == "cpu" and self.on_cuda and cfg.pin_memory
-        mk = lambda: torch.zeros(L.shard_numel, dtype=torch.float32, device=state_dev, pin_memory=pin)  # noqa: E731
-        self.master, self.exp_avg, self.exp_avg_sq = mk(), mk(), mk()
+        self._nvme = None
+        if cfg.offload_optimizer == "nvme":
+            # ZeRO-Infinity tier: state lives in files, host RAM only holds the staging slots (engine/nvme.py)
+            from .nvme import NvmeStateStore, default_nvme_path
+            self._nvme = NvmeStateStore(cfg.nvme_path or default_nvme_path(), self.rank, L.shard_numel,
+                                        buffer_count=cfg.offload_buffer_count, pin=pin, grad_dtype=cfg.accum_dtype,
+                                        chunk=int(os.environ.get("B200ZERO_NVME_CHUNK", 1 << 24)))
+            self.master, self.exp_avg, self.exp_avg_sq = (self._nvme.view(n) for n in ("master", "exp_avg", "exp_avg_sq"))
+            self.exp_avg.zero_()
+            self.exp_avg_sq.zero_()
+        else:
+            mk = lambda: torch.zeros(L.shard_numel, dtype=torch.float32, device=state_dev, pin_memory=pin)  # noqa: E731
+            self.master, self.exp_avg, self.exp_avg_sq = mk(), mk(), mk()
         self.state_device = state_dev
         self.shard_grads = torch.zeros(L.shard_numel, dtype=cfg.accum_dtype, device=dev)
         self.shard_params = self._zeros(L.shard_numel, cd, "shard_params", symmetric=self.stage >= 3)
@@ -533,6 +545,9 @@ class ZeroEngine:
             step_no = self.global_steps - self.skipped_steps + 1
             if self.fused is not None:
                 self.fused.adam_and_publish(lr, step_no)
+            elif self._nvme is not None:
+                from .nvme import nvme_adam_step
+                nvme_adam_step(self, lr, step_no)
             elif self.state_device.type == "cpu" and self.on_cuda:
                 self._offloaded_adam(lr, step_no)
             else:

@@ -194,6 +194,31 @@ int bz_flash_attn_bwd(const void* qkv, const void* out, const float* lse, const 
                       float* workspace, int B, int S, int Hq, int Hk, int head_dim, float softmax_scale,
                       void* stream);
 
+/* ==== libb200zero_host.so (plain C++, no CUDA) ========================================= */
+
+/* ---- H1: AdamW on the host for ZeRO-Offload (AVX-512/AVX2 multiversioned, thread pool).
+ * In place over [0, n); step is 1-based; out (bf16 bits) may be NULL; nthreads <= 0 -> cores/2.
+ *  */
+int bz_host_adamw(float* master, float* m, float* v, const void* grad, int grad_is_bf16, unsigned short* out,
+                  long long n, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                  float grad_scale, int nthreads);
+int bz_host_threads(void);
+
+/* ---- H1b: asynchronous file I/O for the NVMe tier of the optimizer offload ------------
+ * Requests are split into block_bytes slices serviced by a pool of pread/pwrite workers; each
+ * request returns a ticket; bz_aio_wait returns 0, an errno, or -1 for a short read. */
+void* bz_aio_create(int nthreads, long long block_bytes);
+void bz_aio_destroy(void* h);
+int bz_aio_open(const char* path, int create, long long size_bytes, int direct, int* direct_used);
+int bz_aio_close(int fd);
+int bz_aio_fsync(int fd);
+long long bz_aio_read(void* h, int fd, void* buf, long long nbytes, long long offset);
+long long bz_aio_write(void* h, int fd, const void* buf, long long nbytes, long long offset);
+int bz_aio_wait(void* h, long long ticket);
+int bz_aio_wait_all(void* h);
+long long bz_aio_bytes_read(void* h);
+long long bz_aio_bytes_written(void* h);
+
 #ifdef __cplusplus
 }
 #endif

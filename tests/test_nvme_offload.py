@@ -1,0 +1,191 @@
+"""NVMe tier of the optimizer offload (ZeRO-Infinity): the C++ async file-I/O engine and the file-backed
+AdamW step against the in-memory one. Runs entirely on CPU (tmp_path stands in for the NVMe mount)."""
+import os
+
+import pytest
+import torch
+
+from distributed_llm_training_gpu_manager_b200.engine.nvme import AsyncFileIO, NvmeStateStore
+
+
+def test_async_file_io_roundtrip(tmp_path):
+    io = AsyncFileIO(threads=4, block_bytes=1 << 16)
+    n = (1 << 20) + 123                                   # not a multiple of the block size
+    fd = io.open(tmp_path / "blob.bin", size_bytes=n * 4)
+    src = torch.randn(n)
+    half = n // 2
+    t1 = io.write(fd, src[:half].contiguous(), 0)
+    t2 = io.write(fd, src[half:].contiguous(), half * 4)
+    io.wait(t1)
+    io.wait(t2)
+    assert io.bytes_written == n * 4
+    dst = torch.empty(n)
+    io.wait(io.read(fd, dst, 0))
+    assert torch.equal(src, dst)
+    # offset read of a window
+    win = torch.empty(1000)
+    io.wait(io.read(fd, win, 777 * 4))
+    assert torch.equal(win, src[777:1777])
+    # reading past the end is reported, not silently zero-filled
+    past = torch.empty(16)
+    with pytest.raises(OSError):
+        io.wait(io.read(fd, past, n * 4 - 8))
+    io.fsync(fd)
+    io.close()
+    assert os.path.getsize(tmp_path / "blob.bin") == n * 4
+
+
+def test_direct_io_request_falls_back_when_unsupported(tmp_path):
+    io = AsyncFileIO(threads=2)
+    fd = io.open(tmp_path / "d.bin", size_bytes=1 << 16, direct=True)      # tmpfs/overlayfs refuse O_DIRECT: buffered
+    assert fd >= 0 and isinstance(io.direct_used, bool)
+    io.close()
+
+
+def test_store_views_are_coherent_with_streamed_io(tmp_path):
+    st = NvmeStateStore(tmp_path, rank=0, numel=5000, chunk=1024, buffer_count=3)
+    st.view("master").copy_(torch.arange(5000, dtype=torch.float32))       # cold-path write through the mapping
+    chunks = st.chunks()
+    assert len(chunks) == 5 and chunks[-1] == (4096, 5000)
+    st.issue_read(0, *chunks[0])
+    for i, (lo, hi) in enumerate(chunks):
+        if i + 1 < len(chunks):
+            st.issue_read(i + 1, *chunks[i + 1])
+        p, m, v = st.acquire(i, lo, hi)
+        assert torch.equal(p, torch.arange(lo, hi, dtype=torch.float32))
+        p.add_(1.0)
+        m.fill_(float(i))
+        st.release(i, lo, hi)
+    st.drain()
+    assert torch.equal(st.view("master"), torch.arange(5000, dtype=torch.float32) + 1)   # hot-path write seen by the view
+    assert st.view("exp_avg")[4500].item() == 4.0
+    assert st.host_bytes() == 3 * 1024 * (12 + 4 + 2)
+    st.close()
+
+
+def _ds(off, stage, path=None):
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    d = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=stage, offload_optimizer=off, offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-2, warmup_steps=1,
+        wall_clock_breakdown=False))
+    if path is not None and off == "nvme":
+        d["zero_optimization"]["offload_optimizer"]["nvme_path"] = str(path)
+    return d
+
+
+def _train(engine, mc, steps, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    losses = []
+    for _ in range(steps):
+        ids = torch.randint(0, mc.vocab_size, (2, 32), generator=g)
+        engine.backward(engine(ids, ids))
+        losses.append(engine.step()["loss"])
+    return losses
+
+
+@pytest.mark.parametrize("stage", [1, 3])
+def test_nvme_engine_matches_in_memory_engine(tmp_path, stage, monkeypatch):
+    from distributed_llm_training_gpu_manager_b200.engine import initialize
+    from distributed_llm_training_gpu_manager_b200.models import build_torch_model, get_config
+    monkeypatch.setenv("B200ZERO_NVME_CHUNK", "4096")                      # many chunks: the pipeline really cycles its slots
+    mc = get_config("gpt2-tiny")
+    torch.manual_seed(3)
+    a = initialize(build_torch_model(mc), _ds("none", stage), device=torch.device("cpu"))
+    torch.manual_seed(3)
+    b = initialize(build_torch_model(mc), _ds("nvme", stage, tmp_path), device=torch.device("cpu"))
+    assert b._nvme is not None and (tmp_path / "rank0" / "master.f32").exists()
+    assert len(b._nvme.chunks()) > 3
+    la, lb = _train(a, mc, 5), _train(b, mc, 5)
+    assert lb == pytest.approx(la, rel=1e-5)
+    # elements whose gradient is ~0 (1e-12) make m/sqrt(v) ill-conditioned: the C++ and torch AdamW may step them
+    # in opposite directions, so compare in the mean and bound the outliers
+    diff = (a.master - b.master).abs()
+    assert diff.mean().item() < 1e-6 and (diff > 1e-4).float().mean().item() < 1e-3
+    assert torch.allclose(a.exp_avg_sq, b.exp_avg_sq, rtol=1e-4, atol=1e-9)
+    # the state file on disk is the master copy
+    on_disk = torch.from_file(str(tmp_path / "rank0" / "master.f32"), size=b.master.numel(), dtype=torch.float32)
+    assert torch.equal(on_disk, b.master)
+    assert b._nvme.io.bytes_read >= 5 * 3 * 4 * b.master.numel()
+    # host memory held by the tier is the staging slots only
+    assert b._nvme.host_bytes() < 3 * 4 * b.master.numel()
+
+
+def test_nvme_engine_checkpoint_roundtrip(tmp_path, monkeypatch):
+    from distributed_llm_training_gpu_manager_b200.engine import initialize
+    from distributed_llm_training_gpu_manager_b200.models import build_torch_model, get_config
+    monkeypatch.setenv("B200ZERO_NVME_CHUNK", "4096")
+    mc = get_config("gpt2-tiny")
+    torch.manual_seed(5)
+    a = initialize(build_torch_model(mc), _ds("nvme", 2, tmp_path / "nvme_a"), device=torch.device("cpu"))
+    _train(a, mc, 3)
+    a.save_checkpoint(str(tmp_path / "ckpt"), tag="t3")
+    from distributed_llm_training_gpu_manager_b200.engine import checkpoint as ckpt
+    ckpt.wait_for_pending_writes()
+    ref = _train(a, mc, 2, seed=9)
+    torch.manual_seed(6)                                                   # different init: everything must come from the checkpoint
+    b = initialize(build_torch_model(mc), _ds("nvme", 2, tmp_path / "nvme_b"), device=torch.device("cpu"))
+    b.load_checkpoint(str(tmp_path / "ckpt"), "t3")
+    assert b.global_steps == 3
+    got = _train(b, mc, 2, seed=9)
+    assert got == pytest.approx(ref, rel=1e-5)
+
+
+def _nvme_ws2_rank(rank, world, root):
+    import torch
+    from distributed_llm_training_gpu_manager_b200.engine import initialize
+    from distributed_llm_training_gpu_manager_b200.models import build_torch_model, get_config
+    os.environ["B200ZERO_NVME_CHUNK"] = "2048"
+    mc = get_config("gpt2-tiny")
+    out = {}
+    for off in ("none", "nvme"):
+        torch.manual_seed(1)
+        eng = initialize(build_torch_model(mc), _ds(off, 3, root), device=torch.device("cpu"))
+        g = torch.Generator().manual_seed(50 + rank)
+        losses = []
+        for _ in range(4):
+            ids = torch.randint(0, mc.vocab_size, (2, 32), generator=g)
+            eng.backward(eng(ids, ids))
+            losses.append(eng.step()["loss"])
+        out[off] = (losses, eng.full_param("blocks.0.attn_qkv.weight").clone())
+    return out
+
+
+def test_nvme_offload_two_ranks_gloo(tmp_path):
+    from dist_utils import run_ranks
+    outs = run_ranks(_nvme_ws2_rank, 2, (str(tmp_path),))
+    for out in outs:
+        assert out["nvme"][0] == pytest.approx(out["none"][0], rel=1e-5)
+        assert (out["nvme"][1] - out["none"][1]).abs().mean().item() < 1e-6
+    assert (tmp_path / "rank0" / "exp_avg.f32").exists() and (tmp_path / "rank1" / "exp_avg.f32").exists()
+
+
+@pytest.mark.gpu
+def test_nvme_engine_matches_device_engine_gpu(tmp_path, monkeypatch):
+    """CUDA staging path (pinned slots, side-stream D2H/H2D). Written after this round's GPU budget was
+    spent, so opt-in until it has run once on hardware: B200ZERO_TEST_UNVALIDATED=1."""
+    if os.environ.get("B200ZERO_TEST_UNVALIDATED", "0") != "1":
+        pytest.skip("not yet validated on a GPU: set B200ZERO_TEST_UNVALIDATED=1")
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.models import get_config
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+    monkeypatch.setenv("B200ZERO_NVME_CHUNK", str(1 << 16))
+
+    def ds(off):
+        d = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+            zero_stage=3, offload_optimizer=off, offload_param="none", bf16_enabled=True, fp16_enabled=False,
+            train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+            wall_clock_breakdown=False))
+        if off == "nvme":
+            d["zero_optimization"]["offload_optimizer"]["nvme_path"] = str(tmp_path)
+        return d
+    mc = get_config("llama-tiny")
+    a = NativeLlamaEngine(mc, ds("none"), seq_len=256, device=torch.device("cuda", 0))
+    b = NativeLlamaEngine(mc, ds("nvme"), seq_len=256, device=torch.device("cuda", 0))
+    g = torch.Generator().manual_seed(0)
+    for _ in range(3):
+        ids = torch.randint(0, mc.vocab_size, (2, 256), generator=g).cuda()
+        ma, mb = a.train_step(ids, ids), b.train_step(ids, ids)
+        assert ma["loss"] == pytest.approx(mb["loss"], rel=2e-3)
+    diff = (a.master.cpu() - b.master).abs()
+    assert diff.mean().item() < 3e-4 and (diff > 5e-3).float().mean().item() < 1e-3
