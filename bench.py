@@ -13,6 +13,12 @@ Weak scaling: per-GPU work (micro-batch × seq) is fixed as N grows. Synthetic t
 weights (no dataset or checkpoint on the box). Weights (16 GB bf16) and optimizer state (96 GB)
 are far larger than the 126 MB L2, so no explicit L2 flush is needed between steps.
 
+Multi-GPU runs (WORLD_SIZE > 1) execute in one supervised child process per rank (``supervise``): the
+child does all the work and prints the line; the parent watches a heartbeat file. If the default run
+stops making progress (the fused collectives wait on peer flags inside kernels) or dies, it is re-run
+once with ``--comm nccl`` and the line carries a ``"fallback"`` note and ``"comm": "nccl"`` in its
+config. ``B200ZERO_BENCH_SUPERVISE=0`` runs in-process as for N = 1.
+
 ``--impl reference`` runs the unmodified reference from ``baseline/_ref`` through its own public
 API — which can only shell out to a ``deepspeed`` CLI that is not installable offline — and
 reports that outcome.
@@ -51,6 +57,8 @@ def parse_args():
     ap.add_argument("--breakdown", action="store_true", help="after the timed region, run one extra step with per-phase CUDA-event timers")
     ap.add_argument("--torch-profile", default=None, help="write a per-kernel CUDA-time table of one extra step to this file (rank 0)")
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model (result is not a bench value)")
+    ap.add_argument("--worker", action="store_true", help=argparse.SUPPRESS)         # set by supervise()
+    ap.add_argument("--fallback-note", default=None, help=argparse.SUPPRESS)         # set by supervise()
     return ap.parse_args()
 
 
@@ -188,6 +196,113 @@ class ClockSampler:
                 "samples": len(self.samples), "power_w_max": max(s[3] for s in self.samples)}
 
 
+# --------------------------------------------------------------------------- progress watchdog (multi-GPU runs)
+def beat(tag: str) -> None:
+    """Progress mark for the supervising parent (no-op when not supervised)."""
+    path = os.environ.get("B200ZERO_HEARTBEAT_FILE")
+    if path:
+        try:
+            with open(path, "w") as f:
+                f.write(f"{tag} {time.time():.3f}\n")
+        except OSError:
+            pass
+
+
+def _read_beat(path: str):
+    try:
+        with open(path) as f:
+            tag = f.read().split(" ")[0]
+        return tag, os.path.getmtime(path)
+    except (OSError, IndexError):
+        return None, None
+
+
+def supervise(args, argv) -> int:
+    """Multi-GPU runs execute in a child process per rank so that a run which stops making progress
+    (the fused collectives spin on peer flags inside kernels; a lost peer would otherwise hang the job
+    until the caller's limit) is detected and re-run once on the NCCL collectives, with the fallback
+    stated in the JSON line. The child does all the work and prints the line; this parent only watches
+    a heartbeat file and forwards termination."""
+    import signal
+    import subprocess
+    import tempfile
+    rank = int(os.environ.get("RANK", "0"))
+    try:        # keep the kernel library mapped in every process of the job (dlopen only: no CUDA context is created)
+        import ctypes
+        ctypes.CDLL(str(ROOT / "distributed_llm_training_gpu_manager_b200" / "ops" / "libb200zero.so"))
+    except OSError:
+        pass
+    base_port = int(os.environ.get("MASTER_PORT", "29500"))
+    startup_s = float(os.environ.get("B200ZERO_BENCH_STARTUP_S", "360"))
+    quiet_s = float(os.environ.get("B200ZERO_BENCH_QUIET_S", str(150 + 6 * (args.steps + args.warmup))))
+    attempts = [("primary", list(argv), base_port + 113)]
+    if args.comm != "nccl" and args.impl != "nccl":
+        attempts.append(("nccl-fallback", list(argv) + ["--comm", "nccl", "--fallback-note",
+                         "the default (fused-collective) run made no progress or failed; re-run on NCCL collectives"],
+                         base_port + 227))
+    child = {"p": None}
+
+    def on_term(signum, _frame):
+        p = child["p"]
+        if p is not None and p.poll() is None:
+            p.kill()
+        os._exit(128 + signum)
+    signal.signal(signal.SIGTERM, on_term)
+    signal.signal(signal.SIGINT, on_term)
+
+    rc = 1
+    early_exit = []
+    for name, av, port in attempts:
+        fd, hb = tempfile.mkstemp(prefix=f"b200zero_hb_r{rank}_")
+        os.close(fd)
+        env = dict(os.environ, MASTER_PORT=str(port), B200ZERO_HEARTBEAT_FILE=hb)
+        env.pop("TORCHELASTIC_USE_AGENT_STORE", None)      # the children rendezvous on their own store
+        t0 = time.time()
+        p = child["p"] = subprocess.Popen([sys.executable, os.path.abspath(__file__), "--worker"] + av, env=env)
+        verdict = None
+        while verdict is None:
+            try:
+                rc = p.wait(timeout=1.0)
+                verdict = "exited"
+                break
+            except subprocess.TimeoutExpired:
+                pass
+            tag, mtime = _read_beat(hb)
+            now = time.time()
+            if tag == "done":
+                if now - mtime > 45:                        # line printed, teardown stuck: that is a finished run
+                    verdict, rc = "done-stuck", 0
+            elif tag is None or tag == "":
+                if now - t0 > startup_s:
+                    verdict = "no-start"
+            elif now - mtime > (startup_s if tag in ("start", "pg") else quiet_s):
+                verdict = "stalled"
+        if p.poll() is None:
+            p.kill()
+            try:
+                p.wait(timeout=30)
+            except subprocess.TimeoutExpired:
+                pass
+        tag, _ = _read_beat(hb)
+        try:
+            os.unlink(hb)
+        except OSError:
+            pass
+        if verdict == "done-stuck" or (verdict == "exited" and rc == 0) or (tag == "done"):
+            return 0
+        if rank == 0:
+            print(f"[bench] attempt '{name}' {verdict} (rc={rc}, last progress mark: {tag})", file=sys.stderr, flush=True)
+        rc = rc or 1
+        early_exit.append(verdict == "exited" and tag in (None, "", "start") and time.time() - t0 < 90)
+    if early_exit and all(early_exit) and not os.environ.get("B200ZERO_BENCH_FAKE"):
+        # every child died before it got a process group: the child rendezvous itself is the problem —
+        # run in this process on the launcher's own rendezvous, unsupervised
+        if rank == 0:
+            print("[bench] children never reached rendezvous; running in-process", file=sys.stderr, flush=True)
+        return run_ours(args)
+    return rc
+
+
 # --------------------------------------------------------------------------- our arm
 def run_ours(args) -> int:
     import torch
@@ -196,6 +311,7 @@ def run_ours(args) -> int:
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    beat("start")
     if not torch.cuda.is_available():
         if rank == 0:
             print(json.dumps({"metric": METRIC, "value": None, "error": "no CUDA device", "n_gpus": args.gpus}))
@@ -205,6 +321,7 @@ def run_ours(args) -> int:
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+    beat("pg")
 
     from distributed_llm_training_gpu_manager_b200.ai_engine import (DeepSpeedConfig, DeepSpeedLauncher,
                                                                       OffloadDevice, ZeROStage)
@@ -255,9 +372,11 @@ def run_ours(args) -> int:
         torch.cuda.synchronize()
 
     # ---- warm-up ----
+    beat("engine")
     loss_hist = []
     for i in range(args.warmup):
         loss_hist.append(engine.train_step(*dev[i % n_pool])["loss"])
+        beat(f"warmup{i}")
     sync_all()
 
     # ---- device-timed region: exactly K steps ----
@@ -276,6 +395,7 @@ def run_ours(args) -> int:
     sync_all()
     torch.cuda.profiler.stop()
     ms_total = e0.elapsed_time(e1)
+    beat("timed")
     launches = bzlib.launches() - launches0
     clocks = sampler.stop()
 
@@ -291,6 +411,7 @@ def run_ours(args) -> int:
             lab = host[i % n_pool][1].to(device, non_blocking=True)
             m = engine.train_step(ids, lab)
             loss_hist.append(float(m["loss"]))
+            beat(f"e2e{i}")
         sync_all()
         e2e_ms = (time.perf_counter() - t0) * 1e3
 
@@ -369,6 +490,8 @@ def run_ours(args) -> int:
         "final_loss": last["loss"] if last else None,
         "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 1),
     }
+    if args.fallback_note:
+        out["fallback"] = args.fallback_note
     if halt is not None:
         out["spike_to_halt_ms"] = halt
     if breakdown is not None:
@@ -381,6 +504,39 @@ def run_ours(args) -> int:
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()
+    beat("done")
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def _fake_worker(args) -> int:
+    """Test double for the supervisor logic (tests/test_bench_supervisor.py): rendezvous over gloo, then
+    behave as B200ZERO_BENCH_FAKE says — 'ok', 'hang' (fused arm stalls, NCCL arm fine) or 'crash'."""
+    import torch.distributed as dist
+    mode = os.environ["B200ZERO_BENCH_FAKE"]
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    beat("start")
+    if world > 1:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    beat("pg")
+    beat("engine")
+    if args.comm != "nccl":
+        if mode == "hang":
+            time.sleep(3600)
+        if mode == "crash" and rank == world - 1:
+            return 7
+        if mode == "crash":
+            time.sleep(3600)          # the surviving ranks wait on the lost one
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        out = {"metric": METRIC, "value": 1.0, "fake": mode, "comm": args.comm}
+        if args.fallback_note:
+            out["fallback"] = args.fallback_note
+        print(json.dumps(out), flush=True)
+    beat("done")
+    if world > 1:
         dist.destroy_process_group()
     return 0
 
@@ -389,6 +545,11 @@ def main() -> int:
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1 and not args.worker and os.environ.get("B200ZERO_BENCH_SUPERVISE", "1") == "1":
+        return supervise(args, sys.argv[1:])
+    if os.environ.get("B200ZERO_BENCH_FAKE"):
+        return _fake_worker(args)
     return run_ours(args)
 
 

@@ -1,0 +1,43 @@
+"""bench.py runs multi-GPU jobs in a supervised child per rank: a run that stops making progress is
+re-run once on the NCCL collectives and says so in its JSON line. Exercised here with a test double
+for the worker (gloo rendezvous, no GPU)."""
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _run(mode, port):
+    env = dict(os.environ, B200ZERO_BENCH_FAKE=mode, B200ZERO_BENCH_QUIET_S="5", B200ZERO_BENCH_STARTUP_S="60",
+               OMP_NUM_THREADS="1")
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port), str(ROOT / "bench.py"),
+                          "--gpus", "2", "--steps", "2", "--warmup", "1"],
+                         env=env, capture_output=True, text=True, timeout=300, cwd=str(ROOT))
+    lines = [ln for ln in res.stdout.splitlines() if ln.startswith("{")]
+    return res, lines
+
+
+def test_supervised_run_passes_through_when_healthy():
+    from dist_utils import free_port
+    res, lines = _run("ok", free_port())
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert len(lines) == 1
+    out = json.loads(lines[0])
+    assert out["comm"] == "auto" and "fallback" not in out
+
+
+@pytest.mark.parametrize("mode", ["hang", "crash"])
+def test_stalled_or_failed_run_falls_back_to_nccl_once(mode):
+    from dist_utils import free_port
+    res, lines = _run(mode, free_port())
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert len(lines) == 1, res.stdout                      # exactly one JSON line reaches the caller
+    out = json.loads(lines[0])
+    assert out["comm"] == "nccl" and "fallback" in out
+    assert "attempt 'primary'" in res.stderr
