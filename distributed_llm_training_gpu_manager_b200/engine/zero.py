@@ -75,9 +75,24 @@ class PhaseTimers:
         self.enabled, self.cuda = enabled, cuda
         self.totals: Dict[str, float] = {}
         self._open: List[Tuple[str, Any, Any]] = []
+        # B200ZERO_NVTX=1: forward / backward / reduce / allgather / step show up as NVTX ranges in nsys / ncu
+        self.nvtx = bool(cuda) and os.environ.get("B200ZERO_NVTX", "0") == "1"
 
     @contextmanager
     def phase(self, name: str):
+        if self.nvtx:
+            torch.cuda.nvtx.range_push(name)
+            try:
+                with self._timed(name):
+                    yield
+            finally:
+                torch.cuda.nvtx.range_pop()
+        else:
+            with self._timed(name):
+                yield
+
+    @contextmanager
+    def _timed(self, name: str):
         if not self.enabled:
             yield
             return
