@@ -194,6 +194,21 @@ int bz_flash_attn_bwd(const void* qkv, const void* out, const float* lse, const 
                       float* workspace, int B, int S, int Hq, int Hk, int head_dim, float softmax_scale,
                       void* stream);
 
+/* ---- GPT-2 family element-wise ops (csrc/gpt2_ops.cu) ----------
+ * LayerNorm: y = (x - mean) * rstd * w + b over rows of width D (D % 8 == 0, D <= 16384); mean / rstd are
+ * fp32 [T] saved for backward. Backward also produces dw = sum_rows dy * xhat and db = sum_rows dy
+ * (bf16 or fp32, optionally accumulated) through a per-CTA partial workspace of
+ * bz_gpt2_bwd_workspace_floats(T, D) floats. bias + GELU(tanh): y = gelu(x + bias); backward returns dx and
+ * dbias = column sums of the bf16-rounded dx. */
+int bz_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean, float* rstd, int T, int D,
+                     float eps, void* stream);
+long long bz_gpt2_bwd_workspace_floats(int T, int D);
+int bz_layernorm_bwd(const void* x, const void* w, const float* mean, const float* rstd, const void* dy, void* dx,
+                     void* dw, void* db, int dwb_is_f32, int accumulate, float* workspace, int T, int D, void* stream);
+int bz_bias_gelu_fwd(const void* x, const void* bias, void* y, long long T, int F, void* stream);
+int bz_bias_gelu_bwd(const void* x, const void* bias, const void* dy, void* dx, void* dbias, int db_is_f32,
+                     int accumulate, float* workspace, int T, int F, void* stream);
+
 /* ==== libb200zero_host.so (plain C++, no CUDA) ========================================= */
 
 /* ---- H1: AdamW on the host for ZeRO-Offload (AVX-512/AVX2 multiversioned, thread pool).

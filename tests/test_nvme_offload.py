@@ -160,32 +160,45 @@ def test_nvme_offload_two_ranks_gloo(tmp_path):
     assert (tmp_path / "rank0" / "exp_avg.f32").exists() and (tmp_path / "rank1" / "exp_avg.f32").exists()
 
 
-@pytest.mark.gpu
-def test_nvme_engine_matches_device_engine_gpu(tmp_path, monkeypatch):
-    """CUDA staging path (pinned slots, side-stream D2H/H2D). Written after this round's GPU budget was
-    spent, so opt-in until it has run once on hardware: B200ZERO_TEST_UNVALIDATED=1."""
-    if os.environ.get("B200ZERO_TEST_UNVALIDATED", "0") != "1":
-        pytest.skip("not yet validated on a GPU: set B200ZERO_TEST_UNVALIDATED=1")
-    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
-    from distributed_llm_training_gpu_manager_b200.models import get_config
-    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
-    monkeypatch.setenv("B200ZERO_NVME_CHUNK", str(1 << 16))
+_GPU_CHECK = r"""
+import os, sys, torch
+sys.path.insert(0, %r)
+os.environ["B200ZERO_NVME_CHUNK"] = str(1 << 16)
+from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+from distributed_llm_training_gpu_manager_b200.models import get_config
+from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
 
-    def ds(off):
-        d = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
-            zero_stage=3, offload_optimizer=off, offload_param="none", bf16_enabled=True, fp16_enabled=False,
-            train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
-            wall_clock_breakdown=False))
-        if off == "nvme":
-            d["zero_optimization"]["offload_optimizer"]["nvme_path"] = str(tmp_path)
-        return d
-    mc = get_config("llama-tiny")
-    a = NativeLlamaEngine(mc, ds("none"), seq_len=256, device=torch.device("cuda", 0))
-    b = NativeLlamaEngine(mc, ds("nvme"), seq_len=256, device=torch.device("cuda", 0))
-    g = torch.Generator().manual_seed(0)
-    for _ in range(3):
-        ids = torch.randint(0, mc.vocab_size, (2, 256), generator=g).cuda()
-        ma, mb = a.train_step(ids, ids), b.train_step(ids, ids)
-        assert ma["loss"] == pytest.approx(mb["loss"], rel=2e-3)
-    diff = (a.master.cpu() - b.master).abs()
-    assert diff.mean().item() < 3e-4 and (diff > 5e-3).float().mean().item() < 1e-3
+def ds(off):
+    d = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer=off, offload_param="none", bf16_enabled=True, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+        wall_clock_breakdown=False))
+    if off == "nvme":
+        d["zero_optimization"]["offload_optimizer"]["nvme_path"] = %r
+    return d
+mc = get_config("llama-tiny")
+a = NativeLlamaEngine(mc, ds("none"), seq_len=256, device=torch.device("cuda", 0))
+b = NativeLlamaEngine(mc, ds("nvme"), seq_len=256, device=torch.device("cuda", 0))
+assert b._nvme is not None and len(b._nvme.chunks()) > 3
+g = torch.Generator().manual_seed(0)
+for _ in range(3):
+    ids = torch.randint(0, mc.vocab_size, (2, 256), generator=g).cuda()
+    ma, mb = a.train_step(ids, ids), b.train_step(ids, ids)
+    assert abs(ma["loss"] - mb["loss"]) < 2e-3 * abs(ma["loss"]), (ma["loss"], mb["loss"])
+diff = (a.master.cpu() - b.master).abs()
+assert diff.mean().item() < 3e-4 and (diff > 5e-3).float().mean().item() < 1e-3, diff.mean().item()
+print("NVME_GPU_OK")
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="CUDA staging path written after this round's GPU budget was spent: first run on hardware")
+def test_nvme_engine_matches_device_engine_gpu(tmp_path):
+    """Pinned staging slots + side-stream D2H/H2D of the NVMe tier, in a child process with its own time limit."""
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = str(Path(__file__).resolve().parent.parent)
+    res = subprocess.run([sys.executable, "-c", _GPU_CHECK % (root, str(tmp_path))], capture_output=True, text=True,
+                         timeout=600)
+    assert "NVME_GPU_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
