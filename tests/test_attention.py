@@ -76,3 +76,69 @@ def test_flash_bwd_matches_autograd_oracle(B, S, Hq, Hk):
         scale = b_.abs().max().item() + 1e-6
         assert (a - b_).abs().max().item() / scale < 4e-2, (name, (a - b_).abs().max().item(), scale)
         assert (a - b_).abs().mean().item() / (b_.abs().mean().item() + 1e-9) < 2e-2, name
+
+
+_V3_CHECK = r"""
+import sys, torch
+sys.path.insert(0, %r)
+from distributed_llm_training_gpu_manager_b200.ops import attention as A
+from distributed_llm_training_gpu_manager_b200.ops import flash as F
+torch.manual_seed(1)
+hd = 128
+for B, S, Hq, Hk in ((1, 128, 1, 1), (1, 256, 2, 1), (2, 512, 8, 2), (1, 1024, 4, 4), (1, 4096, 2, 1)):
+    qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
+    out, lse = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=3)
+    torch.cuda.synchronize()
+    assert int(F._err_flag[str(qkv.device)].item()) == 0, "shared-memory segment not aligned"
+    out2, lse2 = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=2)
+    ref = A.attention_ref(qkv, B, S, Hq, Hk, hd)
+    err = (out.float() - ref).abs().max().item()
+    assert err < 3e-2, ("v3 vs oracle", B, S, Hq, Hk, err)
+    assert (out.float() - ref).abs().mean().item() < 2e-3
+    assert torch.allclose(lse, lse2, rtol=1e-3, atol=2e-2), ("lse v3 vs v2", B, S)
+# growing maximum along kv: the lazy-rescale branch with PVs in flight
+B, S, Hq, Hk = 1, 1024, 2, 1
+qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda")
+qkv[:, Hq * hd:(Hq + Hk) * hd] *= torch.linspace(0.2, 6.0, S, device="cuda")[:, None]
+qkv[:, :Hq * hd] *= 3.0
+qkv = qkv.bfloat16()
+out, _ = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=3)
+ref = A.attention_ref(qkv, B, S, Hq, Hk, hd)
+assert (out.float() - ref).abs().max().item() < 6e-2, "rescale path"
+# timing, for the record (CUDA events, after warm-up)
+B, S, Hq, Hk = 2, 4096, 32, 8
+qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
+res = {}
+for ver in (2, 3):
+    for _ in range(3):
+        F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=ver)
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); s.record()
+    for _ in range(10):
+        F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=ver)
+    e.record(); torch.cuda.synchronize()
+    ms = s.elapsed_time(e) / 10
+    res[ver] = (ms, 4 * B * Hq * S * S * hd / 2 / ms / 1e9)
+print("FLASH_V3_OK", {k: (round(a, 4), round(b, 1)) for k, (a, b) in res.items()})
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="v3 forward written after this round's GPU budget was spent: first run on hardware")
+def test_flash_fwd_v3_matches_reference():
+    """Child process with its own time limit: a fault or hang in the not-yet-validated kernel cannot touch
+    the CUDA context of the tests collected after this one."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = str(Path(__file__).resolve().parent.parent)
+    res = subprocess.run([sys.executable, "-c", _V3_CHECK % root], capture_output=True, text=True, timeout=300,
+                         env=dict(os.environ))
+    out_dir = Path(root) / "gpurun_out"
+    try:
+        out_dir.mkdir(exist_ok=True)
+        (out_dir / "flash_v3_check.log").write_text(res.stdout[-4000:] + "\n--- stderr ---\n" + res.stderr[-4000:])
+    except OSError:
+        pass
+    assert "FLASH_V3_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
