@@ -2,7 +2,6 @@
 differential test against /root/reference when it is mounted)."""
 import importlib.util
 import json
-import math
 import os
 import statistics
 import sys

@@ -1,5 +1,4 @@
 """LR schedules, fp16 loss scaler, elastic batch solver, engine config parsing, fleet sampler."""
-import math
 
 import pytest
 

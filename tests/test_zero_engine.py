@@ -1,11 +1,8 @@
 """ZeRO engine on CPU/gloo, world_size 2: sharded training must reproduce the single-process
 result (this is the oracle tier for the GPU kernels — SURVEY.md §4 item 2), checkpoints must
 round-trip and re-partition, and the monitor → halt → rollback → resume loop must work."""
-import copy
 import json
 import os
-import sys
-import subprocess
 
 import pytest
 import torch
