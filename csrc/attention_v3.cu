@@ -41,6 +41,22 @@ __device__ __forceinline__ void f3_st_shared_v4(uint32_t addr, uint32_t a, uint3
   asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+// 2^x on the FMA pipe (no MUFU): round-to-nearest split x = n + f, f in [-0.5, 0.5], degree-3 minimax polynomial
+// for 2^f (max relative error 7.5e-5, far below bf16's 3.9e-3), n added straight into the exponent field.
+// The B200 SFU does 16 ex2/clk/SM against 128 FMA lanes/clk/SM, and a 128x128 score tile needs 16 384
+// exponentials = 1 024 SFU cycles — as long as the tensor core needs for the tile's two GEMMs. Sending every
+// POLY-th element through this routine moves the exponentials off the critical pipe.
+__device__ __forceinline__ float f3_exp2_poly(float x) {
+  x = fmaxf(x, -126.f);
+  const float xr = x + 12582912.f;            // 1.5 * 2^23: round(x) lands in the low mantissa bits
+  const float f = x - (xr - 12582912.f);
+  float p = fmaf(f, 0.05517165f, 0.24261113f);
+  p = fmaf(f, p, 0.69326097f);
+  p = fmaf(f, p, 0.99992806f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(xr) << 23));
+}
+
+template <int POLY>   // 0: every exponential on the SFU; n > 0: elements with (index % n) == n - 1 use f3_exp2_poly
 __global__ void __launch_bounds__(F3_THREADS, 1)
 flash_fwd_v3_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out, float* __restrict__ lse,
                     int* __restrict__ error_flag, int B, int S, int Hq, int Hk, int ld_out, float scale_log2) {
@@ -216,8 +232,10 @@ flash_fwd_v3_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
       uint32_t pk[32];
 #pragma unroll
       for (int e = 0; e < 64; e += 2) {
-        const float p0 = fast_exp2(fmaf(__uint_as_float(sv[e]), scale_log2, neg_m));
-        const float p1 = fast_exp2(fmaf(__uint_as_float(sv[e + 1]), scale_log2, neg_m));
+        const float x0 = fmaf(__uint_as_float(sv[e]), scale_log2, neg_m);
+        const float x1 = fmaf(__uint_as_float(sv[e + 1]), scale_log2, neg_m);
+        const float p0 = (POLY > 0 && (e % POLY) == POLY - 1) ? f3_exp2_poly(x0) : fast_exp2(x0);
+        const float p1 = (POLY > 0 && ((e + 1) % POLY) == POLY - 1) ? f3_exp2_poly(x1) : fast_exp2(x1);
         rs += p0 + p1;
         pk[e >> 1] = pack_bf16x2(p0, p1);
       }
@@ -270,24 +288,36 @@ flash_fwd_v3_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
 using namespace bz;
 
 // Same contract as bz_flash_attn_fwd. error_flag (device int, may be NULL) is set to 1 if the kernel refused
-// to run because its shared-memory segment was not aligned as required.
+// to run because its shared-memory segment was not aligned as required. poly_stride: 0 = all exponentials on
+// the SFU; 2..8 = every poly_stride-th one on the FMA pipe (4 balances the two pipes on B200).
 extern "C" int bz_flash_attn_fwd_v3(const void* qkv, void* out, float* lse, int* error_flag, int B, int S, int Hq,
-                                    int Hk, int head_dim, float softmax_scale, void* stream) {
+                                    int Hk, int head_dim, float softmax_scale, int poly_stride, void* stream) {
   BZ_REQUIRE(head_dim == F3_HD, "flash_attn_fwd_v3: head_dim %d unsupported (128 only)", head_dim);
   BZ_REQUIRE(S % F3_BM == 0 && S > 0, "flash_attn_fwd_v3: seq_len %d must be a multiple of %d", S, F3_BM);
   BZ_REQUIRE(Hq % Hk == 0, "flash_attn_fwd_v3: Hq=%d not a multiple of Hkv=%d", Hq, Hk);
+  BZ_REQUIRE(poly_stride == 0 || poly_stride == 2 || poly_stride == 4 || poly_stride == 8,
+             "flash_attn_fwd_v3: poly_stride %d not in {0, 2, 4, 8}", poly_stride);
   const int ld = (Hq + 2 * Hk) * F3_HD;
   CUtensorMap tm;
   if (int rc = make_tmap_2d_bf16(&tm, qkv, (uint64_t)B * S, ld, ld, 128, 64)) return rc;
   static bool attr_done = false;
   if (!attr_done) {
-    BZ_CUDA_CHECK(cudaFuncSetAttribute(flash_fwd_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
+    BZ_CUDA_CHECK(cudaFuncSetAttribute(flash_fwd_v3_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
+    BZ_CUDA_CHECK(cudaFuncSetAttribute(flash_fwd_v3_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
+    BZ_CUDA_CHECK(cudaFuncSetAttribute(flash_fwd_v3_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
+    BZ_CUDA_CHECK(cudaFuncSetAttribute(flash_fwd_v3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
     attr_done = true;
   }
   const int grid = (S / F3_BM) * Hq * B;
   const float scale_log2 = softmax_scale * 1.4426950408889634f;
-  flash_fwd_v3_kernel<<<grid, F3_THREADS, F3_SMEM, (cudaStream_t)stream>>>(tm, (__nv_bfloat16*)out, lse, error_flag, B,
-                                                                         S, Hq, Hk, Hq * F3_HD, scale_log2);
+  cudaStream_t st = (cudaStream_t)stream;
+  __nv_bfloat16* o = (__nv_bfloat16*)out;
+  switch (poly_stride) {
+    case 0: flash_fwd_v3_kernel<0><<<grid, F3_THREADS, F3_SMEM, st>>>(tm, o, lse, error_flag, B, S, Hq, Hk, Hq * F3_HD, scale_log2); break;
+    case 2: flash_fwd_v3_kernel<2><<<grid, F3_THREADS, F3_SMEM, st>>>(tm, o, lse, error_flag, B, S, Hq, Hk, Hq * F3_HD, scale_log2); break;
+    case 4: flash_fwd_v3_kernel<4><<<grid, F3_THREADS, F3_SMEM, st>>>(tm, o, lse, error_flag, B, S, Hq, Hk, Hq * F3_HD, scale_log2); break;
+    default: flash_fwd_v3_kernel<8><<<grid, F3_THREADS, F3_SMEM, st>>>(tm, o, lse, error_flag, B, S, Hq, Hk, Hq * F3_HD, scale_log2); break;
+  }
   BZ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -12,7 +12,7 @@ _lib.register("bz_flash_attn_fwd", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.i3
 
 
 _lib.register("bz_flash_attn_fwd_v3", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.i32, _lib.i32, _lib.i32,
-                                                 _lib.i32, _lib.i32, _lib.f32, _lib.vp])
+                                                 _lib.i32, _lib.i32, _lib.f32, _lib.i32, _lib.vp])
 _err_flag = {}
 
 
@@ -20,7 +20,8 @@ def flash_fwd(qkv: torch.Tensor, B: int, S: int, Hq: int, Hk: int, hd: int,
               want_lse: bool = True, version: Optional[int] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     """Causal GQA attention forward. Returns (out [T, Hq*hd] bf16, lse [Hq, T] fp32).
     ``version`` (default ``$B200ZERO_FLASH_FWD`` or 2): 3 selects the double-buffered-P kernel of
-    ``csrc/attention_v3.cu`` (opt-in until validated on hardware)."""
+    ``csrc/attention_v3.cu`` (opt-in until validated on hardware); 32 / 34 / 38 = the same kernel with every
+    2nd / 4th / 8th exponential evaluated on the FMA pipe instead of the SFU."""
     import os
     T = B * S
     assert qkv.is_contiguous() and qkv.shape == (T, (Hq + 2 * Hk) * hd) and qkv.dtype == torch.bfloat16
@@ -29,12 +30,13 @@ def flash_fwd(qkv: torch.Tensor, B: int, S: int, Hq: int, Hk: int, hd: int,
     L = _lib.load(required=True)
     if version is None:
         version = int(os.environ.get("B200ZERO_FLASH_FWD", "2"))
-    if version == 3:
+    if version in (3, 32, 34, 38):
         key = str(qkv.device)
         if key not in _err_flag:
             _err_flag[key] = torch.zeros(1, dtype=torch.int32, device=qkv.device)
         _lib.check(L.bz_flash_attn_fwd_v3(qkv.data_ptr(), out.data_ptr(), _lib.ptr(lse), _err_flag[key].data_ptr(), B, S,
-                                          Hq, Hk, hd, hd ** -0.5, _lib.stream()), "flash_attn_fwd_v3")
+                                          Hq, Hk, hd, hd ** -0.5, version % 10 if version > 3 else 0, _lib.stream()),
+                   "flash_attn_fwd_v3")
         return out, lse
     _lib.check(L.bz_flash_attn_fwd(qkv.data_ptr(), out.data_ptr(), _lib.ptr(lse), B, S, Hq, Hk, hd, hd ** -0.5,
                                    _lib.stream()), "flash_attn_fwd")

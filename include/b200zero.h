@@ -196,9 +196,11 @@ int bz_flash_attn_bwd(const void* qkv, const void* out, const float* lse, const 
 
 /* ---- K6 forward, v3 (opt-in): P double-buffered so exp/pack of block j+1 overlaps O += P_j V_j; same
  * contract as bz_flash_attn_fwd. error_flag (device int, may be NULL) becomes 1 if the kernel declined to run
- * because its dynamic shared-memory segment was not 1024-aligned (it needs 226.25 KB of the 227 KB). */
+ * because its dynamic shared-memory segment was not 1024-aligned (it needs 226.25 KB of the 227 KB).
+ * poly_stride in {0, 2, 4, 8}: every poly_stride-th exponential is evaluated on the FMA pipe (degree-3
+ * polynomial, rel. error 7.5e-5) instead of the SFU; 0 = all on the SFU. */
 int bz_flash_attn_fwd_v3(const void* qkv, void* out, float* lse, int* error_flag, int B, int S, int Hq, int Hk,
-                         int head_dim, float softmax_scale, void* stream);
+                         int head_dim, float softmax_scale, int poly_stride, void* stream);
 
 /* ---- GPT-2 family element-wise ops (csrc/gpt2_ops.cu) ----------
  * LayerNorm: y = (x - mean) * rstd * w + b over rows of width D (D % 8 == 0, D <= 16384); mean / rstd are

@@ -96,6 +96,10 @@ for B, S, Hq, Hk in ((1, 128, 1, 1), (1, 256, 2, 1), (2, 512, 8, 2), (1, 1024, 4
     assert err < 3e-2, ("v3 vs oracle", B, S, Hq, Hk, err)
     assert (out.float() - ref).abs().mean().item() < 2e-3
     assert torch.allclose(lse, lse2, rtol=1e-3, atol=2e-2), ("lse v3 vs v2", B, S)
+    for ver in (32, 34, 38):                       # FMA-pipe exponentials mixed in
+        outp, lsep = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=ver)
+        assert (outp.float() - ref).abs().max().item() < 3e-2, ("poly", ver, B, S)
+        assert torch.allclose(lsep, lse2, rtol=1e-3, atol=2e-2), ("lse poly", ver, B, S)
 # growing maximum along kv: the lazy-rescale branch with PVs in flight
 B, S, Hq, Hk = 1, 1024, 2, 1
 qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda")
@@ -109,7 +113,7 @@ assert (out.float() - ref).abs().max().item() < 6e-2, "rescale path"
 B, S, Hq, Hk = 2, 4096, 32, 8
 qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
 res = {}
-for ver in (2, 3):
+for ver in (2, 3, 38, 34, 32):
     for _ in range(3):
         F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=ver)
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
