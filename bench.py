@@ -255,7 +255,9 @@ def supervise(args, argv) -> int:
     for name, av, port in attempts:
         fd, hb = tempfile.mkstemp(prefix=f"b200zero_hb_r{rank}_")
         os.close(fd)
-        env = dict(os.environ, MASTER_PORT=str(port), B200ZERO_HEARTBEAT_FILE=hb)
+        fd, park = tempfile.mkstemp(prefix=f"b200zero_result_r{rank}_")
+        os.close(fd)
+        env = dict(os.environ, MASTER_PORT=str(port), B200ZERO_HEARTBEAT_FILE=hb, B200ZERO_BENCH_RESULT_FILE=park)
         env.pop("TORCHELASTIC_USE_AGENT_STORE", None)      # the children rendezvous on their own store
         t0 = time.time()
         p = child["p"] = subprocess.Popen([sys.executable, os.path.abspath(__file__), "--worker"] + av, env=env)
@@ -269,7 +271,7 @@ def supervise(args, argv) -> int:
                 pass
             tag, mtime = _read_beat(hb)
             now = time.time()
-            if tag == "done":
+            if tag in ("done", "printed"):
                 if now - mtime > 45:                        # line printed, teardown stuck: that is a finished run
                     verdict, rc = "done-stuck", 0
             elif tag is None or tag == "":
@@ -284,11 +286,24 @@ def supervise(args, argv) -> int:
             except subprocess.TimeoutExpired:
                 pass
         tag, _ = _read_beat(hb)
+        parked = None
         try:
-            os.unlink(hb)
+            with open(park) as f:
+                parked = f.read().strip()
         except OSError:
             pass
-        if verdict == "done-stuck" or (verdict == "exited" and rc == 0) or (tag == "done"):
+        for path in (hb, park):
+            try:
+                os.unlink(path)
+            except OSError:
+                pass
+        if verdict == "done-stuck" or (verdict == "exited" and rc == 0) or tag in ("done", "printed"):
+            return 0
+        if tag == "probe":
+            # the timed regions finished on every rank and the result was parked; only the spike-to-halt probe
+            # that follows them did not complete — report the measurement rather than re-running it
+            if rank == 0 and parked:
+                print(parked, flush=True)
             return 0
         if rank == 0:
             print(f"[bench] attempt '{name}' {verdict} (rc={rc}, last progress mark: {tag})", file=sys.stderr, flush=True)
@@ -437,32 +452,11 @@ def run_ours(args) -> int:
             with open(args.torch_profile, "w") as f:
                 f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))
 
-    # ---- spike-to-halt: after every timed region; a failure here never costs the throughput line ----
-    halt = None
-    if not args.skip_halt:
-        try:
-            sync_all()
-            halt = measure_spike_to_halt(engine, dev[0], [x for x in loss_hist if x == x])
-        except Exception as exc:  # noqa: BLE001
-            halt = {"error": f"{type(exc).__name__}: {exc}"}
-    halt_ms = [0.0, 0.0, 0.0]
-    if halt and "error" not in halt:
-        halt_ms = [halt["nan_grad"]["from_backward_end"], halt["loss_spike_x50"]["from_backward_end"],
-                   halt["loss_spike_x50"]["from_forward_end"]]
-
     # ---- max over ranks ----
-    t = torch.tensor([ms_total, e2e_ms or 0.0] + halt_ms, device=device, dtype=torch.float64)
+    t = torch.tensor([ms_total, e2e_ms or 0.0], device=device, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, e2e_total = float(t[0]), float(t[1])
-    if halt and "error" not in halt:
-        halt = {"nan_grad_ms": round(float(t[2]), 3), "loss_spike_x50_ms": round(float(t[3]), 3),
-                "loss_spike_x50_from_forward_end_ms": round(float(t[4]), 2),
-                "actions": {"nan_grad": halt["nan_grad"]["action"], "loss_spike_x50": halt["loss_spike_x50"]["action"]},
-                "alerts": {"nan_grad": halt["nan_grad"]["alerts"], "loss_spike_x50": halt["loss_spike_x50"]["alerts"]},
-                "definition": "max over ranks; device-synchronised end of the offending backward pass -> halt/rollback "
-                              "decision in hand (stats all-reduce + pinned D2H + LossSpikeMonitor + HaltPolicy); the "
-                              "parameter update of a non-finite step is skipped on the device inside that same step"}
     tokens_per_step = MB * S * world
     value = tokens_per_step * args.steps / (ms_total / 1e3)
     flops_tok = mcfg.flops_per_token(S, recompute=False)      # model FLOPs (6·N + attention): recompute not counted
@@ -492,16 +486,46 @@ def run_ours(args) -> int:
     }
     if args.fallback_note:
         out["fallback"] = args.fallback_note
-    if halt is not None:
-        out["spike_to_halt_ms"] = halt
     if breakdown is not None:
         out["breakdown_ms"] = {k: round(v, 2) for k, v in breakdown.items()}
     if e2e_ms is not None:
         out["e2e"] = {"value": round(tokens_per_step * args.steps / (e2e_total / 1e3), 1), "unit": "tokens/s",
                       "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                       "ms_per_step": round(e2e_total / args.steps, 2)}
+    # ---- spike-to-halt: after every timed region. The throughput result is parked first, so a probe that
+    #      stalls or fails costs only its own key (the supervising parent prints the parked line). ----
+    if not args.skip_halt:
+        park = os.environ.get("B200ZERO_BENCH_RESULT_FILE")
+        if park and rank == 0:
+            try:
+                with open(park, "w") as f:
+                    json.dump(dict(out, spike_to_halt_ms={"error": "probe did not complete"}), f)
+            except OSError:
+                pass
+        beat("probe")
+        halt, halt_ms = None, [0.0, 0.0, 0.0]
+        try:
+            sync_all()
+            halt = measure_spike_to_halt(engine, dev[0], [x for x in loss_hist if x == x])
+            halt_ms = [halt["nan_grad"]["from_backward_end"], halt["loss_spike_x50"]["from_backward_end"],
+                       halt["loss_spike_x50"]["from_forward_end"]]
+        except Exception as exc:  # noqa: BLE001
+            halt = {"error": f"{type(exc).__name__}: {exc}"}
+        t = torch.tensor(halt_ms, device=device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if "error" not in halt:
+            halt = {"nan_grad_ms": round(float(t[0]), 3), "loss_spike_x50_ms": round(float(t[1]), 3),
+                    "loss_spike_x50_from_forward_end_ms": round(float(t[2]), 2),
+                    "actions": {"nan_grad": halt["nan_grad"]["action"], "loss_spike_x50": halt["loss_spike_x50"]["action"]},
+                    "alerts": {"nan_grad": halt["nan_grad"]["alerts"], "loss_spike_x50": halt["loss_spike_x50"]["alerts"]},
+                    "definition": "max over ranks; device-synchronised end of the offending backward pass -> halt/rollback "
+                                  "decision in hand (stats all-reduce + pinned D2H + LossSpikeMonitor + HaltPolicy); the "
+                                  "parameter update of a non-finite step is skipped on the device inside that same step"}
+        out["spike_to_halt_ms"] = halt
     if rank == 0:
         print(json.dumps(out), flush=True)
+    beat("printed")
     if world > 1:
         dist.barrier()
     beat("done")
@@ -530,10 +554,17 @@ def _fake_worker(args) -> int:
             time.sleep(3600)          # the surviving ranks wait on the lost one
     if world > 1:
         dist.barrier()
+    out = {"metric": METRIC, "value": 1.0, "fake": mode, "comm": args.comm}
+    if args.fallback_note:
+        out["fallback"] = args.fallback_note
+    if mode == "probe-hang":          # timed regions done, result parked, then the spike-to-halt probe never returns
+        park = os.environ.get("B200ZERO_BENCH_RESULT_FILE")
+        if park and rank == 0:
+            with open(park, "w") as f:
+                json.dump(dict(out, spike_to_halt_ms={"error": "probe did not complete"}), f)
+        beat("probe")
+        time.sleep(3600)
     if rank == 0:
-        out = {"metric": METRIC, "value": 1.0, "fake": mode, "comm": args.comm}
-        if args.fallback_note:
-            out["fallback"] = args.fallback_note
         print(json.dumps(out), flush=True)
     beat("done")
     if world > 1:

@@ -41,3 +41,15 @@ def test_stalled_or_failed_run_falls_back_to_nccl_once(mode):
     out = json.loads(lines[0])
     assert out["comm"] == "nccl" and "fallback" in out
     assert "attempt 'primary'" in res.stderr
+
+
+def test_stalled_probe_keeps_the_measured_result():
+    """The spike-to-halt probe runs after the timed regions; if it never returns, the parked throughput line is
+    printed (once) instead of re-running the benchmark on the fallback path."""
+    from dist_utils import free_port
+    res, lines = _run("probe-hang", free_port())
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert len(lines) == 1, res.stdout
+    out = json.loads(lines[0])
+    assert out["comm"] == "auto" and "fallback" not in out
+    assert out["spike_to_halt_ms"] == {"error": "probe did not complete"}
