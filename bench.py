@@ -235,11 +235,12 @@ def supervise(args, argv) -> int:
     base_port = int(os.environ.get("MASTER_PORT", "29500"))
     startup_s = float(os.environ.get("B200ZERO_BENCH_STARTUP_S", "360"))
     quiet_s = float(os.environ.get("B200ZERO_BENCH_QUIET_S", str(150 + 6 * (args.steps + args.warmup))))
-    attempts = [("primary", list(argv), base_port + 113)]
+    sign = 1 if base_port + 227 < 65000 else -1             # stay inside the valid port range
+    attempts = [("primary", list(argv), base_port + sign * 113)]
     if args.comm != "nccl" and args.impl != "nccl":
         attempts.append(("nccl-fallback", list(argv) + ["--comm", "nccl", "--fallback-note",
                          "the default (fused-collective) run made no progress or failed; re-run on NCCL collectives"],
-                         base_port + 227))
+                         base_port + sign * 227))
     child = {"p": None}
 
     def on_term(signum, _frame):
