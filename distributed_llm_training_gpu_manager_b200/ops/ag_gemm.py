@@ -40,5 +40,26 @@ def ag_linear_fwd(x: torch.Tensor, shard_ptrs, w_full: torch.Tensor, rank: int, 
     return out
 
 
+_lib.register("bz_ag_gemm_dgrad_bf16", _lib.i32, [_lib.vp, C.POINTER(_lib.vp), _lib.vp, _lib.vp, _lib.vp, _lib.i32,
+                                                  _lib.i32, _lib.i32, _lib.i32, _lib.i32, _lib.i32, _lib.i32, _lib.i32,
+                                                  _lib.vp])
+
+
+def ag_linear_dgrad(dy: torch.Tensor, shard_ptrs, w_full: torch.Tensor, rank: int, ws: int,
+                    out: Optional[torch.Tensor] = None, cta_group: int = 0) -> torch.Tensor:
+    """``dx = dy @ gather(W)`` for a row-partitioned ``W`` [N, K] (the partitioned dimension is the GEMM's
+    reduction dimension; ``csrc/ag_gemm_dgrad.cu``). ``w_full`` receives the gathered weight."""
+    M, N = dy.shape
+    K = w_full.shape[1]
+    assert w_full.shape == (N, K) and w_full.is_contiguous() and dy.stride(1) == 1
+    out = out if out is not None else torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
+    L = _lib.load(required=True)
+    rc = L.bz_ag_gemm_dgrad_bf16(dy.data_ptr(), shard_ptrs, w_full.data_ptr(), out.data_ptr(),
+                                 _chunk_scratch(dy.device).data_ptr(), M, N, K, dy.stride(0), out.stride(0), rank, ws,
+                                 cta_group, _lib.stream())
+    _lib.check(rc, "ag_gemm_dgrad")
+    return out
+
+
 def ptr_array(ptrs: Sequence[int]):
     return (C.c_void_p * len(ptrs))(*ptrs)

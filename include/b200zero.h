@@ -184,6 +184,12 @@ int bz_ag_gemm_max_tiles(void);
 int bz_ag_gemm_bf16(const void* X, void* const* shard_ptrs, void* Wfull, void* Y, void* chunk_ready, int M, int N,
                     int K, int ldx, int ldc, int rank, int ws, int cta_group, void* stream);
 
+/* ---- K2, dgrad flavour: dX[M,K] = dY[M,N] · W[N,K] with W row-partitioned over `ws` ranks (the gathered
+ * dimension is the reduction dimension). Same peer/chunk protocol as bz_ag_gemm_bf16; the k-loop consumes the
+ * 256-row chunks in arrival order, W is read MN-major (no transposed copy). chunk_ready: >= ceil(N/256) uint32. */
+int bz_ag_gemm_dgrad_bf16(const void* dY, void* const* shard_ptrs, void* Wfull, void* dX, void* chunk_ready, int M,
+                          int N, int K, int ldy, int ldc, int rank, int ws, int cta_group, void* stream);
+
 /* ---- K6: flash attention backward ---------------------------------------------------
  * dqkv (same fused layout as qkv) from qkv, out, lse (from the forward) and dout.
  * workspace: bz_flash_attn_bwd_workspace_floats(B,S,Hq) floats (fp32 dQ accumulator +

@@ -10,6 +10,7 @@ if [ "${1:-single}" = "single" ]; then
   # the child-process tests report xfail/xpass; --runxfail turns a failure into a visible failure
   TMO=600 run gpt2_ops   python -m pytest tests/test_gpt2_ops.py -m gpu -q --runxfail
   TMO=600 run flash_v3   python -m pytest tests/test_attention.py -m gpu -q --runxfail -k v3
+  TMO=900 run ag_dgrad   python -m pytest tests/test_ag_gemm_dgrad.py -m gpu -q --runxfail
   TMO=600 run nvme_gpu   python -m pytest tests/test_nvme_offload.py -m gpu -q --runxfail
   TMO=900 run bench_n1   python bench.py --steps 6 --warmup 3
   B200ZERO_FLASH_FWD=3  TMO=900 run bench_n1_flash3   python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
