@@ -207,6 +207,11 @@ class NativeLlamaEngine(ZeroEngine):
         self._ag_fused = (self.fused is not None and self.stage >= 3 and self.pooled_params
                           and os.environ.get("B200ZERO_AG_GEMM", "1") == "1")
         self._ag_ptrs: Dict[str, Any] = {}
+        # K2 dgrad flavour (opt-in until it has run on hardware): with nothing recomputed every weight is used
+        # exactly once in backward — by its dgrad — so that GEMM gathers it in-kernel and backward needs no
+        # bulk gather / prefetch stream at all.
+        self._ag_dgrad = (self._ag_fused and self.recompute in ("none", "light")
+                          and os.environ.get("B200ZERO_AG_DGRAD", "0") == "1")
         self._act_offload = (ActivationOffloader(self.device)
                              if (self.cfg.cpu_checkpointing and self.on_cuda) else None)
 
@@ -251,6 +256,20 @@ class NativeLlamaEngine(ZeroEngine):
             ptrs = self.fused._ptrs_for(self.shard_params[spec.shard_offset:spec.shard_offset + spec.shard_numel])
             self._ag_ptrs[full] = ptrs
         return ag_linear_fwd(x, ptrs, w, self.rank, self.world_size)
+
+    def _dgrad(self, l: int, name: str, dy: torch.Tensor, ag: bool) -> torch.Tensor:
+        """dx = dy · W; when ``ag`` the weight is all-gathered inside the GEMM kernel (K2, dgrad flavour)."""
+        w = self._w(l, name)
+        if not ag:
+            return G.linear_dgrad(dy, w)
+        from ..ops.ag_gemm import ag_linear_dgrad
+        full = f"blocks.{l}.{name}.weight"
+        ptrs = self._ag_ptrs.get(full)
+        if ptrs is None:
+            spec = self.layout.by_name[full]
+            ptrs = self.fused._ptrs_for(self.shard_params[spec.shard_offset:spec.shard_offset + spec.shard_numel])
+            self._ag_ptrs[full] = ptrs
+        return ag_linear_dgrad(dy, ptrs, w, self.rank, self.world_size)
 
     def _begin_block(self, l: int) -> bool:
         """Make block ``l``'s parameters available. Returns True when the GEMMs must gather their own
@@ -308,10 +327,14 @@ class NativeLlamaEngine(ZeroEngine):
         c = self.mcfg
         S = self.seq_len
         Hq, Hk, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        agd = False
         if sv is None:
             _, sv = self._block_fwd(l, x, keep=True)                  # full recompute
         else:
-            self._begin_block_bwd(l)
+            if self._ag_dgrad and "gu" in sv:
+                agd = self._begin_block(l)                             # True: the dgrad GEMMs gather their own weights
+            else:
+                self._begin_block_bwd(l)
             if "gu" not in sv:                                        # selective: redo gate|up GEMM + SwiGLU only
                 sv["gu"] = G.linear_fwd(sv["h2"], self._w(l, "w_gate_up"))
             if "act" not in sv:                                       # light: SwiGLU only
@@ -319,21 +342,21 @@ class NativeLlamaEngine(ZeroEngine):
         adt = dict(accumulate=acc)
         # MLP
         G.linear_wgrad(dx2, sv["act"], out=self._gw(l, "w_down"), **adt)
-        dact = G.linear_dgrad(dx2, self._w(l, "w_down"))
+        dact = self._dgrad(l, "w_down", dx2, agd)
         dgu = E.swiglu_bwd(sv["gu"], dact)
         del dact
         G.linear_wgrad(dgu, sv["h2"], out=self._gw(l, "w_gate_up"), **adt)
-        dh2 = G.linear_dgrad(dgu, self._w(l, "w_gate_up"))
+        dh2 = self._dgrad(l, "w_gate_up", dgu, agd)
         del dgu
         dx1, _ = E.rmsnorm_bwd(sv["x1"], self._w(l, "ffn_norm"), dh2, c.norm_eps, rstd=sv["rstd2"], dres=dx2,
                                dw_out=self._gw(l, "ffn_norm"), dw_accumulate=acc, dx_out=dh2)
         # attention
         G.linear_wgrad(dx1, sv["attn"], out=self._gw(l, "wo"), **adt)
-        dattn = G.linear_dgrad(dx1, self._w(l, "wo"))
+        dattn = self._dgrad(l, "wo", dx1, agd)
         dqkv = A.attention_bwd(sv["actx"], dattn)
         E.rope_(dqkv, S, Hq + Hk, hd, c.rope_theta, inverse=True)
         G.linear_wgrad(dqkv, sv["h1"], out=self._gw(l, "wqkv"), **adt)
-        dh1 = G.linear_dgrad(dqkv, self._w(l, "wqkv"))
+        dh1 = self._dgrad(l, "wqkv", dqkv, agd)
         dx, _ = E.rmsnorm_bwd(x, self._w(l, "attn_norm"), dh1, c.norm_eps, rstd=sv["rstd1"], dres=dx1,
                               dw_out=self._gw(l, "attn_norm"), dw_accumulate=acc, dx_out=dh1)
         return dx
@@ -420,7 +443,8 @@ class NativeLlamaEngine(ZeroEngine):
                                   rstd=sv["rstd_f"], dw_out=self.grad_view("final_norm.weight"), dw_accumulate=acc)
             for l in range(L - 1, -1, -1):
                 ui = l + 1
-                if self.pooled_params and ui - 1 >= 1 and (not self._ag_fused or self.recompute != "full"):
+                if (self.pooled_params and ui - 1 >= 1 and (not self._ag_fused or self.recompute != "full")
+                        and not self._ag_dgrad):
                     self._prefetch(ui - 1)
                 if self.pooled_grads and self.on_cuda:
                     evt = self._gslot_free_evt[(ui - 1) % 2]

@@ -23,6 +23,8 @@ else
   # followed by two bench runs that never finished ("Tried and backed out")
   TMO=600 run bench_default   $TR --master-port 29601 bench.py --gpus $N --steps 8 --warmup 3
   TMO=600 run bench_nccl      $TR --master-port 29602 bench.py --gpus $N --steps 4 --warmup 3 --comm nccl --skip-e2e
+  B200ZERO_TEST_AG_DGRAD=1 TMO=600 run ag_dgrad_engine python -m pytest tests/test_fused_comm.py -m gpu -q -k dgrad
+  B200ZERO_AG_DGRAD=1 TMO=600 run bench_ag_dgrad $TR --master-port 29606 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e
   B200ZERO_TEST_NVLS=1 TMO=600 run nvls_test python -m pytest tests/test_fused_comm.py -m gpu -q -k nvls
   B200ZERO_NVLS=1 TMO=600 run bench_nvls $TR --master-port 29603 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e
   TMO=600 run bench_after_nvls $TR --master-port 29604 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e

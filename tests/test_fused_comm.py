@@ -135,10 +135,11 @@ def test_adam_push_and_pull_allgather_emulated():
             assert torch.equal(dst[fo:fo + n], params[r][fo:fo + n]) or not part
 
 
-def _fused_vs_nccl_rank(rank, world, stage, gas=1, nvls=False):
+def _fused_vs_nccl_rank(rank, world, stage, gas=1, nvls=False, ag_dgrad=False):
     import os
     import torch.distributed as dist
     os.environ["B200ZERO_NVLS"] = "1" if nvls else "0"
+    os.environ["B200ZERO_AG_DGRAD"] = "1" if ag_dgrad else "0"
     from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
     from distributed_llm_training_gpu_manager_b200.models import get_config
     from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
@@ -183,6 +184,21 @@ def test_nvls_multimem_path_matches_nccl(stage):
         pytest.skip("no NVLS multicast support on this box")
     for out in outs:
         assert out["nvls_launches"] > 0
+        assert out["fused"][0] == pytest.approx(out["nccl"][0], rel=2e-3)
+        assert out["fused"][1] == pytest.approx(out["nccl"][1], rel=2e-2)
+        assert torch.allclose(out["fused"][2], out["nccl"][2], rtol=2e-2, atol=2e-3)
+
+
+@pytest.mark.multigpu
+def test_ag_gemm_dgrad_in_engine_matches_nccl():
+    """B200ZERO_AG_DGRAD=1: backward gathers every weight inside its dgrad GEMM (no bulk gather, no prefetch).
+    Opt-in (B200ZERO_TEST_AG_DGRAD=1) until the kernel has run on hardware."""
+    import os
+    if os.environ.get("B200ZERO_TEST_AG_DGRAD", "0") != "1":
+        pytest.skip("dgrad all-gather->GEMM is opt-in: set B200ZERO_TEST_AG_DGRAD=1")
+    from dist_utils import run_ranks_nccl
+    world = min(torch.cuda.device_count(), 4)
+    for out in run_ranks_nccl(_fused_vs_nccl_rank, world, (3, 1, False, True), timeout=240):
         assert out["fused"][0] == pytest.approx(out["nccl"][0], rel=2e-3)
         assert out["fused"][1] == pytest.approx(out["nccl"][1], rel=2e-2)
         assert torch.allclose(out["fused"][2], out["nccl"][2], rtol=2e-2, atol=2e-3)
