@@ -203,6 +203,17 @@ extern "C" int bz_adamw(float* master, float* m, float* v, const void* grad, int
   return 0;
 }
 
+// The optimizer can be overlapped with the next forward pass (engine option): its CTAs then share SMs with
+// persistent GEMM CTAs that need ~200 KB of shared memory, so it must not pin the SM's L1/shared split to the
+// L1-heavy default (same reasoning as comm_kernels_setup_once in fused_comm.cu).
+extern "C" int bz_adamw_prefer_max_shared_carveout(void) {
+  BZ_CUDA_CHECK(cudaFuncSetAttribute(adamw_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
+  BZ_CUDA_CHECK(cudaFuncSetAttribute(adamw_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
+  return 0;
+}
+
 extern "C" int bz_sumsq_workspace_floats(void) { return MAX_PARTIALS; }
 
 extern "C" int bz_sumsq(const void* g, int g_is_f32, long long n, float* workspace, float* out, int accumulate,

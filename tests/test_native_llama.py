@@ -105,3 +105,44 @@ def test_capacity_planning_70b_on_8_b200():
     # the 8B headline config: one GPU holds everything, light recompute fits (measured peak 153 GB)
     s8, a8 = static_bytes(c8, 1), activation_bytes(c8, 2, 4096)
     assert 120 * GB < s8["device_total"] < 140 * GB and s8["device_total"] + a8["light"] < 172 * GB
+
+
+_OVERLAP_CHECK = r"""
+import os, sys, torch
+sys.path.insert(0, %r)
+from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+from distributed_llm_training_gpu_manager_b200.models import get_config
+from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+    zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=True, fp16_enabled=False,
+    train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+    wall_clock_breakdown=False))
+mc = get_config("llama-tiny")
+res = {}
+for flag in ("0", "1"):
+    os.environ["B200ZERO_ADAM_OVERLAP"] = flag
+    eng = NativeLlamaEngine(mc, ds, seq_len=256, device=torch.device("cuda", 0), seed=3)
+    assert (eng._adam_stream is not None) == (flag == "1"), "overlap switch"
+    g = torch.Generator().manual_seed(0)
+    losses = []
+    for _ in range(6):
+        ids = torch.randint(0, mc.vocab_size, (2, 256), generator=g).cuda()
+        losses.append(eng.train_step(ids, ids)["loss"])
+    res[flag] = (losses, eng.full_param("blocks.1.w_down.weight").clone(), eng.full_param("lm_head.weight").clone())
+assert res["0"][0] == res["1"][0], (res["0"][0], res["1"][0])
+assert torch.equal(res["0"][1], res["1"][1]) and torch.equal(res["0"][2], res["1"][2])
+print("ADAM_OVERLAP_OK")
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="optimizer/forward overlap written after this round's GPU budget was spent")
+def test_adam_overlap_is_bit_identical():
+    """AdamW of step t on a side stream, unit by unit, while step t+1's forward runs: same arithmetic, so losses
+    and weights must be bit-identical to the serial schedule. Child process: not yet validated on hardware."""
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = str(Path(__file__).resolve().parent.parent)
+    res = subprocess.run([sys.executable, "-c", _OVERLAP_CHECK % root], capture_output=True, text=True, timeout=600)
+    assert "ADAM_OVERLAP_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
