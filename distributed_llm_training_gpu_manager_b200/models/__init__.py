@@ -1,4 +1,4 @@
-from .configs import PRESETS, ModelConfig, get_config
+from .configs import PRESET_MODELS, PRESETS, ModelConfig, get_config
 
 
 def build_torch_model(cfg: ModelConfig):
@@ -12,4 +12,4 @@ def build_torch_model(cfg: ModelConfig):
     raise ValueError(f"unknown model family {cfg.family!r}")
 
 
-__all__ = ["PRESETS", "ModelConfig", "get_config", "build_torch_model"]
+__all__ = ["PRESETS", "PRESET_MODELS", "ModelConfig", "get_config", "build_torch_model"]

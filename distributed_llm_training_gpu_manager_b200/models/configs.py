@@ -71,7 +71,14 @@ PRESETS: Dict[str, ModelConfig] = {
     "llama3-8b": ModelConfig("llama", 128256, 4096, 32, 32, 8, 14336, 8192),
     # BASELINE.json config 5
     "llama3-70b": ModelConfig("llama", 128256, 8192, 80, 64, 8, 28672, 8192),
+    # the sizes behind the launcher's `7b` / `13b` presets (ref ai_engine/deepspeed_launcher.py:373-392):
+    # Llama-2 shapes — multi-head attention (kv heads = heads), head_dim 128, so they run on the same kernels
+    "llama2-7b": ModelConfig("llama", 32000, 4096, 32, 32, 32, 11008, 4096, rope_theta=10000.0),
+    "llama2-13b": ModelConfig("llama", 32000, 5120, 40, 40, 40, 13824, 4096, rope_theta=10000.0),
 }
+
+# launcher preset name -> architecture used when a job is started from that preset without naming a model
+PRESET_MODELS: Dict[str, str] = {"7b": "llama2-7b", "13b": "llama2-13b", "70b": "llama3-70b"}
 
 
 def get_config(name: str, **overrides) -> ModelConfig:

@@ -83,3 +83,18 @@ def test_fleet_sampler_ring_buffer():
     fs.stop()
     assert 1 <= len(fs.snapshots) <= 5 and fs.latest().total_gpus == 2
     assert set(fs.clocks_summary()) >= {"sm_mhz", "sm_max_mhz", "reasons"}
+
+
+def test_preset_architectures_cover_the_launcher_presets():
+    """The launcher's 7b / 13b / 70b presets (ref ai_engine/deepspeed_launcher.py:369-407) each map to an
+    architecture whose size matches its name and whose head_dim is the 128 the attention kernels serve."""
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.models import PRESET_MODELS, get_config
+    presets = DeepSpeedLauncher.presets()
+    assert set(PRESET_MODELS) == set(presets)
+    want = {"7b": 6.7e9, "13b": 13.0e9, "70b": 70.6e9}
+    for name, model in PRESET_MODELS.items():
+        cfg = get_config(model)
+        assert abs(cfg.num_params() - want[name]) / want[name] < 0.01, (name, cfg.num_params())
+        assert cfg.head_dim == 128 and cfg.n_heads % cfg.n_kv_heads == 0
+        assert cfg.ffn % 8 == 0 and cfg.padded_vocab % 256 == 0
