@@ -82,6 +82,7 @@ PRESET_MODELS: Dict[str, str] = {"7b": "llama2-7b", "13b": "llama2-13b", "70b": 
 
 
 def get_config(name: str, **overrides) -> ModelConfig:
+    name = PRESET_MODELS.get(name, name)       # "7b" / "13b" / "70b" (launcher preset names) are accepted as aliases
     if name not in PRESETS:
         raise KeyError(f"unknown model preset {name!r}; available: {sorted(PRESETS)}")
     cfg = PRESETS[name]
