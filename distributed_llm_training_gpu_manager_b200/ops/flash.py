@@ -49,9 +49,15 @@ _lib.register("bz_flash_attn_bwd", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.vp
 _ws = {}
 
 
+_lib.register("bz_flash_attn_bwd_v3", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.i32,
+                                                 _lib.i32, _lib.i32, _lib.i32, _lib.i32, _lib.f32, _lib.vp])
+
+
 def flash_bwd(qkv: torch.Tensor, out: torch.Tensor, lse: torch.Tensor, dout: torch.Tensor, B: int, S: int, Hq: int,
-              Hk: int, hd: int, dqkv: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Gradient w.r.t. the fused QKV buffer (same layout as ``qkv``)."""
+              Hk: int, hd: int, dqkv: Optional[torch.Tensor] = None, version: Optional[int] = None) -> torch.Tensor:
+    """Gradient w.r.t. the fused QKV buffer (same layout as ``qkv``). ``version`` (default ``$B200ZERO_FLASH_BWD`` or
+    2): 3 selects the pipelined schedule of ``csrc/attention_bwd_v3.cu`` (opt-in until validated on hardware)."""
+    import os
     T = B * S
     L = _lib.load(required=True)
     if dqkv is None:
@@ -61,6 +67,16 @@ def flash_bwd(qkv: torch.Tensor, out: torch.Tensor, lse: torch.Tensor, dout: tor
     if key not in _ws or _ws[key].numel() < need:
         _ws[key] = torch.empty(need, dtype=torch.float32, device=qkv.device)
     assert dout.is_contiguous() and out.is_contiguous() and dqkv.is_contiguous()
+    if version is None:
+        version = int(os.environ.get("B200ZERO_FLASH_BWD", "2"))
+    if version == 3:
+        if key not in _err_flag:
+            _err_flag[key] = torch.zeros(1, dtype=torch.int32, device=qkv.device)
+        _lib.check(L.bz_flash_attn_bwd_v3(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), dout.data_ptr(), dqkv.data_ptr(),
+                                          _ws[key].data_ptr(), _err_flag[key].data_ptr(), B, S, Hq, Hk, hd, hd ** -0.5,
+                                          _lib.stream()), "flash_attn_bwd_v3")
+        _lib.add_launches(2)
+        return dqkv
     _lib.check(L.bz_flash_attn_bwd(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), dout.data_ptr(), dqkv.data_ptr(),
                                    _ws[key].data_ptr(), B, S, Hq, Hk, hd, hd ** -0.5, _lib.stream()), "flash_attn_bwd")
     _lib.add_launches(2)

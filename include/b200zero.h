@@ -226,6 +226,12 @@ int bz_bias_gelu_fwd(const void* x, const void* bias, void* y, long long T, int 
 int bz_bias_gelu_bwd(const void* x, const void* bias, const void* dy, void* dx, void* dbias, int db_is_f32,
                      int accumulate, float* workspace, int T, int F, void* stream);
 
+/* ---- K6 backward, v3 (opt-in): S^T of tile i+1 issued behind dV of tile i, dP^T of tile i+1 behind dS(i),
+ * dQ^T of tile i-1 staged after dS(i); same contract and workspace as bz_flash_attn_bwd. */
+int bz_flash_attn_bwd_v3(const void* qkv, const void* out, const float* lse, const void* dout, void* dqkv,
+                         float* workspace, int* error_flag, int B, int S, int Hq, int Hk, int head_dim,
+                         float softmax_scale, void* stream);
+
 /* ==== libb200zero_host.so (plain C++, no CUDA) ========================================= */
 
 /* ---- H1: AdamW on the host for ZeRO-Offload (AVX-512/AVX2 multiversioned, thread pool).

@@ -146,3 +146,66 @@ def test_flash_fwd_v3_matches_reference():
     except OSError:
         pass
     assert "FLASH_V3_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
+
+
+_BWD_V3_CHECK = r"""
+import sys, torch
+sys.path.insert(0, %r)
+from distributed_llm_training_gpu_manager_b200.ops import attention as A
+from distributed_llm_training_gpu_manager_b200.ops import flash as F
+torch.manual_seed(3)
+hd = 128
+for B, S, Hq, Hk in ((1, 128, 1, 1), (1, 256, 2, 1), (2, 512, 8, 2), (1, 1024, 4, 4), (1, 2048, 4, 1)):
+    qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
+    dout = torch.randn(B * S, Hq * hd, device="cuda").bfloat16()
+    out, lse = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=2)
+    d3 = F.flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd, version=3).clone()
+    torch.cuda.synchronize()
+    assert int(F._err_flag[str(qkv.device)].item()) == 0, "shared-memory segment not aligned"
+    d2 = F.flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd, version=2).clone()
+    x = qkv.float().requires_grad_()
+    (A.attention_ref(x, B, S, Hq, Hk, hd) * dout.float()).sum().backward()
+    ref = x.grad
+    for name, lo, hi in (("dq", 0, Hq * hd), ("dk", Hq * hd, (Hq + Hk) * hd), ("dv", (Hq + Hk) * hd, (Hq + 2 * Hk) * hd)):
+        a, b_ = d3[:, lo:hi].float(), ref[:, lo:hi]
+        scale = b_.abs().max().item() + 1e-6
+        assert (a - b_).abs().max().item() / scale < 4e-2, (name, B, S, Hq, Hk, (a - b_).abs().max().item(), scale)
+        assert (a - b_).abs().mean().item() / (b_.abs().mean().item() + 1e-9) < 2e-2, (name, B, S)
+    # same arithmetic per element as v2 (dK / dV accumulate in the same order; dQ is a sum of fp32 atomics-free reductions)
+    assert torch.allclose(d3.float(), d2.float(), rtol=2e-2, atol=2e-2), ("v3 vs v2", B, S)
+B, S, Hq, Hk = 2, 4096, 32, 8
+qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
+dout = torch.randn(B * S, Hq * hd, device="cuda").bfloat16()
+out, lse = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=2)
+res = {}
+for ver in (2, 3):
+    for _ in range(3):
+        F.flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd, version=ver)
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); s.record()
+    for _ in range(10):
+        F.flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd, version=ver)
+    e.record(); torch.cuda.synchronize()
+    ms = s.elapsed_time(e) / 10
+    res[ver] = (round(ms, 4), round(2.5 * 4 * B * Hq * S * S * hd / 2 / ms / 1e9, 1))
+print("FLASH_BWD_V3_OK", res)
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="pipelined backward written after this round's GPU budget was spent: first run on hardware")
+def test_flash_bwd_v3_matches_reference():
+    """Child process with its own time limit (see test_flash_fwd_v3_matches_reference)."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = str(Path(__file__).resolve().parent.parent)
+    res = subprocess.run([sys.executable, "-c", _BWD_V3_CHECK % root], capture_output=True, text=True, timeout=300,
+                         env=dict(os.environ))
+    try:
+        (Path(root) / "gpurun_out").mkdir(exist_ok=True)
+        (Path(root) / "gpurun_out" / "flash_bwd_v3_check.log").write_text(res.stdout[-4000:] + "\n--- stderr ---\n" + res.stderr[-4000:])
+    except OSError:
+        pass
+    assert "FLASH_BWD_V3_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
