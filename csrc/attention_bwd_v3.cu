@@ -214,6 +214,7 @@ flash_bwd_v3_kernel(const __grid_constant__ CUtensorMap tmKV, const __grid_const
       const int qi = i0 + k % per_head;
       if (ct == 0) tma_store_wait_read<0>();                 // the previous reduce has read the staging buffer
       asm volatile("bar.sync 2, 256;" ::: "memory");
+      tc_fence_after();
       {
         uint32_t v[32];
         tmem_ld_32x32(tm_dq + lane_off + c0, v);
