@@ -31,6 +31,18 @@ def _workspace(device, nfloats: int, tag: str) -> torch.Tensor:
 
 
 # ------------------------------------------------------------------ RMSNorm
+_lib.register("bz_rmsnorm_fwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.i32, _lib.i32,
+                                              _lib.f32, _lib.vp])
+_lib.register("bz_rmsnorm_bwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.vp, _lib.i32,
+                                              _lib.i32, _lib.vp, _lib.i32, _lib.i32, _lib.f32, _lib.vp])
+
+
+def _rmsnorm_version() -> int:
+    """2 = the row-ahead-prefetch kernels of csrc/elementwise_v2.cu (opt-in until validated on hardware)."""
+    import os
+    return int(os.environ.get("B200ZERO_RMSNORM", "1"))
+
+
 def rmsnorm_ref(x, w, eps, delta=None):
     xo = x.float() + (delta.float() if delta is not None else 0)
     if delta is not None:
@@ -50,8 +62,9 @@ def rmsnorm_fwd(x: torch.Tensor, w: torch.Tensor, eps: float = 1e-5, delta: Opti
     xo = torch.empty_like(x) if delta is not None else None
     rstd = torch.empty(T, dtype=torch.float32, device=x.device) if want_rstd else None
     L = _lib.load()
-    _lib.check(L.bz_rmsnorm_fwd(x.data_ptr(), _lib.ptr(delta), w.data_ptr(), _lib.ptr(xo), y.data_ptr(),
-                                _lib.ptr(rstd), T, D, eps, _lib.stream()), "rmsnorm_fwd")
+    fn = L.bz_rmsnorm_fwd_v2 if _rmsnorm_version() == 2 else L.bz_rmsnorm_fwd
+    _lib.check(fn(x.data_ptr(), _lib.ptr(delta), w.data_ptr(), _lib.ptr(xo), y.data_ptr(),
+                  _lib.ptr(rstd), T, D, eps, _lib.stream()), "rmsnorm_fwd")
     return y, rstd, xo
 
 
@@ -88,9 +101,10 @@ def rmsnorm_bwd(x: torch.Tensor, w: torch.Tensor, dy: torch.Tensor, eps: float =
         dw_out = torch.empty(D, dtype=torch.float32, device=x.device)
         dw_accumulate = False
     ws = _workspace(x.device, L.bz_rmsnorm_bwd_workspace_floats(T, D), "rms_bwd")
-    _lib.check(L.bz_rmsnorm_bwd(x.data_ptr(), w.data_ptr(), _lib.ptr(rstd), dy.data_ptr(), _lib.ptr(dres),
-                                dx.data_ptr(), dw_out.data_ptr(), int(dw_out.dtype == torch.float32),
-                                int(dw_accumulate), ws.data_ptr(), T, D, eps, _lib.stream()), "rmsnorm_bwd")
+    fn = L.bz_rmsnorm_bwd_v2 if _rmsnorm_version() == 2 else L.bz_rmsnorm_bwd
+    _lib.check(fn(x.data_ptr(), w.data_ptr(), _lib.ptr(rstd), dy.data_ptr(), _lib.ptr(dres),
+                  dx.data_ptr(), dw_out.data_ptr(), int(dw_out.dtype == torch.float32),
+                  int(dw_accumulate), ws.data_ptr(), T, D, eps, _lib.stream()), "rmsnorm_bwd")
     _lib.add_launches(1)  # two kernels behind one entry point
     return dx, dw_out
 

@@ -211,6 +211,14 @@ int bz_flash_attn_bwd(const void* qkv, const void* out, const float* lse, const 
 int bz_flash_attn_fwd_v3(const void* qkv, void* out, float* lse, int* error_flag, int B, int S, int Hq, int Hk,
                          int head_dim, float softmax_scale, int poly_stride, void* stream);
 
+/* ---- K5, v2 (opt-in): RMSNorm forward / backward with the next row's loads issued before the current row's
+ * reductions (twice the bytes in flight per SM); same contracts, workspace and bit-identical results. */
+int bz_rmsnorm_fwd_v2(const void* x, const void* delta, const void* w, void* x_out, void* y, float* rstd, int T, int D,
+                      float eps, void* stream);
+int bz_rmsnorm_bwd_v2(const void* x, const void* w, const float* rstd, const void* dy, const void* dres, void* dx,
+                      void* dw, int dw_is_f32, int dw_accumulate, float* workspace, int T, int D, float eps,
+                      void* stream);
+
 /* ---- GPT-2 family element-wise ops (csrc/gpt2_ops.cu) ----------
  * LayerNorm: y = (x - mean) * rstd * w + b over rows of width D (D % 8 == 0, D <= 16384); mean / rstd are
  * fp32 [T] saved for backward. Backward also produces dw = sum_rows dy * xhat and db = sum_rows dy

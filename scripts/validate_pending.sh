@@ -8,6 +8,7 @@ mkdir -p gpurun_out
 run() { local name=$1; shift; echo "=== $name"; timeout "${TMO:-600}" "$@" > "gpurun_out/pending_$name.log" 2>&1; echo "rc=$? ($name)"; tail -4 "gpurun_out/pending_$name.log"; }
 if [ "${1:-single}" = "single" ]; then
   # the child-process tests report xfail/xpass; --runxfail turns a failure into a visible failure
+  TMO=600 run rmsnorm_v2 python -m pytest tests/test_elementwise.py -m gpu -q --runxfail -k v2
   TMO=600 run gpt2_ops   python -m pytest tests/test_gpt2_ops.py -m gpu -q --runxfail
   TMO=600 run flash_v3   python -m pytest tests/test_attention.py -m gpu -q --runxfail -k v3
   TMO=900 run ag_dgrad   python -m pytest tests/test_ag_gemm_dgrad.py -m gpu -q --runxfail
@@ -16,6 +17,7 @@ if [ "${1:-single}" = "single" ]; then
   TMO=900 run bench_n1   python bench.py --steps 6 --warmup 3
   B200ZERO_ADAM_OVERLAP=1 TMO=900 run bench_n1_adam_overlap python bench.py --steps 6 --warmup 3 --skip-halt
   B200ZERO_FLASH_BWD=3  TMO=900 run bench_n1_flashbwd3 python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
+  B200ZERO_RMSNORM=2    TMO=900 run bench_n1_rmsnorm2 python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_FLASH_FWD=3  TMO=900 run bench_n1_flash3   python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_FLASH_FWD=34 TMO=900 run bench_n1_flash34  python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_GPT2_NATIVE_OPS=1 TMO=600 run gpt2xl_native_ops python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt --model gpt2-xl --zero-stage 2 --seq-len 1024 --micro-batch 8 --engine module

@@ -151,3 +151,75 @@ def test_casts(dev):
     f = torch.empty(1001, device=dev)
     O.cast_to_f32(b, f)
     assert torch.equal(f, b.float())
+
+
+_RMS_V2_CHECK = r"""
+import os, sys, torch
+sys.path.insert(0, %r)
+from distributed_llm_training_gpu_manager_b200.ops import elementwise as E
+torch.manual_seed(0)
+def run(ver, T, D, with_delta, with_dres):
+    os.environ["B200ZERO_RMSNORM"] = str(ver)
+    g = torch.Generator(device="cuda").manual_seed(T * 7 + D)
+    x = torch.randn(T, D, device="cuda", generator=g).bfloat16()
+    w = (1 + 0.1 * torch.randn(D, device="cuda", generator=g)).bfloat16()
+    dl = torch.randn(T, D, device="cuda", generator=g).bfloat16() if with_delta else None
+    dy = torch.randn(T, D, device="cuda", generator=g).bfloat16()
+    dr = torch.randn(T, D, device="cuda", generator=g).bfloat16() if with_dres else None
+    y, rstd, xo = E.rmsnorm_fwd(x, w, 1e-5, delta=dl)
+    xin = xo if xo is not None else x
+    dw = torch.zeros(D, device="cuda", dtype=torch.float32)
+    dx, dw = E.rmsnorm_bwd(xin, w, dy, 1e-5, rstd=rstd, dres=dr, dw_out=dw)
+    dx2, _ = E.rmsnorm_bwd(xin, w, dy, 1e-5, rstd=None, dres=dr)          # statistics recomputed in the kernel
+    torch.cuda.synchronize()
+    return y, rstd, xo, dx, dw, dx2
+for T, D in ((64, 128), (300, 1600), (1000, 4096), (513, 8192), (8192, 4096)):
+    for with_delta, with_dres in ((False, False), (True, True)):
+        a = run(1, T, D, with_delta, with_dres)
+        b = run(2, T, D, with_delta, with_dres)
+        for name, u, v in zip(("y", "rstd", "xo", "dx", "dw", "dx_norstd"), a, b):
+            if u is None:
+                assert v is None
+                continue
+            assert torch.equal(u, v), (name, T, D, with_delta, (u.float() - v.float()).abs().max().item())
+# timing on the Llama-3-8B shape
+T, D = 8192, 4096
+x = torch.randn(T, D, device="cuda").bfloat16(); w = torch.ones(D, device="cuda").bfloat16()
+dy = torch.randn(T, D, device="cuda").bfloat16(); dr = torch.randn(T, D, device="cuda").bfloat16()
+dw = torch.zeros(D, device="cuda", dtype=torch.float32)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+res = {}
+for ver in (1, 2):
+    os.environ["B200ZERO_RMSNORM"] = str(ver)
+    _, rstd, _ = E.rmsnorm_fwd(x, w, 1e-5)
+    for name, fn in (("fwd", lambda: E.rmsnorm_fwd(x, w, 1e-5)),
+                     ("bwd", lambda: E.rmsnorm_bwd(x, w, dy, 1e-5, rstd=rstd, dres=dr, dw_out=dw))):
+        ts = []
+        for _ in range(8):
+            flush.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record(); fn(); e.record(); torch.cuda.synchronize()
+            ts.append(s.elapsed_time(e))
+        res[(name, ver)] = round(sorted(ts)[len(ts) // 2] * 1e3, 1)
+print("RMSNORM_V2_OK us:", res)
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="prefetching RMSNorm kernels written after this round's GPU budget was spent")
+def test_rmsnorm_v2_is_bit_identical_to_v1():
+    """Same arithmetic in the same order, only the loads are issued a row ahead: outputs must be bit-identical.
+    Child process: not yet validated on hardware."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = str(Path(__file__).resolve().parent.parent)
+    res = subprocess.run([sys.executable, "-c", _RMS_V2_CHECK % root], capture_output=True, text=True, timeout=300,
+                         env=dict(os.environ))
+    try:
+        (Path(root) / "gpurun_out").mkdir(exist_ok=True)
+        (Path(root) / "gpurun_out" / "rmsnorm_v2_check.log").write_text(res.stdout[-4000:] + "\n--- stderr ---\n" + res.stderr[-4000:])
+    except OSError:
+        pass
+    assert "RMSNORM_V2_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
