@@ -37,6 +37,16 @@ _lib.register("bz_rmsnorm_bwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.vp
                                               _lib.i32, _lib.vp, _lib.i32, _lib.i32, _lib.f32, _lib.vp])
 
 
+_lib.register("bz_swiglu_fwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.i64, _lib.i32, _lib.vp])
+_lib.register("bz_swiglu_bwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.i64, _lib.i32, _lib.vp])
+
+
+def _swiglu_version() -> int:
+    """2 = the division-free SwiGLU kernels of csrc/elementwise_v2.cu (opt-in until validated on hardware)."""
+    import os
+    return int(os.environ.get("B200ZERO_SWIGLU", "1"))
+
+
 def _rmsnorm_version() -> int:
     """2 = the row-ahead-prefetch kernels of csrc/elementwise_v2.cu (opt-in until validated on hardware)."""
     import os
@@ -168,7 +178,8 @@ def swiglu_fwd(gu: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
         return r
     out = out if out is not None else torch.empty((T, F), dtype=gu.dtype, device=gu.device)
     L = _lib.load()
-    _lib.check(L.bz_swiglu_fwd(gu.data_ptr(), out.data_ptr(), T, F, _lib.stream()), "swiglu_fwd")
+    fn = L.bz_swiglu_fwd_v2 if _swiglu_version() == 2 else L.bz_swiglu_fwd
+    _lib.check(fn(gu.data_ptr(), out.data_ptr(), T, F, _lib.stream()), "swiglu_fwd")
     return out
 
 
@@ -185,7 +196,8 @@ def swiglu_bwd(gu: torch.Tensor, dact: torch.Tensor, out: Optional[torch.Tensor]
         return r
     out = out if out is not None else torch.empty_like(gu)
     L = _lib.load()
-    _lib.check(L.bz_swiglu_bwd(gu.data_ptr(), dact.data_ptr(), out.data_ptr(), T, F, _lib.stream()), "swiglu_bwd")
+    fn = L.bz_swiglu_bwd_v2 if _swiglu_version() == 2 else L.bz_swiglu_bwd
+    _lib.check(fn(gu.data_ptr(), dact.data_ptr(), out.data_ptr(), T, F, _lib.stream()), "swiglu_bwd")
     return out
 
 

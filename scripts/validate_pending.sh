@@ -17,7 +17,7 @@ if [ "${1:-single}" = "single" ]; then
   TMO=900 run bench_n1   python bench.py --steps 6 --warmup 3
   B200ZERO_ADAM_OVERLAP=1 TMO=900 run bench_n1_adam_overlap python bench.py --steps 6 --warmup 3 --skip-halt
   B200ZERO_FLASH_BWD=3  TMO=900 run bench_n1_flashbwd3 python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
-  B200ZERO_RMSNORM=2    TMO=900 run bench_n1_rmsnorm2 python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
+  B200ZERO_RMSNORM=2 B200ZERO_SWIGLU=2 TMO=900 run bench_n1_elementwise2 python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_FLASH_FWD=3  TMO=900 run bench_n1_flash3   python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_FLASH_FWD=34 TMO=900 run bench_n1_flash34  python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_GPT2_NATIVE_OPS=1 TMO=600 run gpt2xl_native_ops python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt --model gpt2-xl --zero-stage 2 --seq-len 1024 --micro-batch 8 --engine module
