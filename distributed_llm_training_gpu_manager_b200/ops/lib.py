@@ -67,6 +67,7 @@ _SIGNATURES = {
     "bz_fused_reduce_scatter_mc": (i32, [C.POINTER(vp), C.POINTER(vp), vp, vp, i32, vp, i32, f32, vp, vp, vp, vp,
                                          C.c_uint, i32, i32, i32, i32, i32, vp]),
     "bz_pull_allgather": (i32, [C.POINTER(vp), vp, i32, vp, i32, i32, i32, vp]),
+    "bz_pull_allgather_v2": (i32, [C.POINTER(vp), vp, i32, vp, i32, i32, i32, vp]),
 }
 
 

@@ -37,6 +37,7 @@ class FusedComm:
         rs_ctas = rs_ctas or int(os.environ.get("B200ZERO_RS_CTAS", "128"))
         adam_ctas = adam_ctas or int(os.environ.get("B200ZERO_ADAM_CTAS", "148"))
         self.nvls_ctas = int(os.environ.get("B200ZERO_NVLS_CTAS", "32"))
+        self.pull_version = int(os.environ.get("B200ZERO_PULL_AG", "1"))   # 2: division-free kernel (fused_comm_v2.cu)
         self.use_fused_gather = os.environ.get("B200ZERO_FUSED_GATHER", "1") == "1"
         self.use_fused_rs = os.environ.get("B200ZERO_FUSED_RS", "1") == "1"
         assert engine.on_cuda, "fused communication needs GPUs"
@@ -124,9 +125,10 @@ class FusedComm:
         e = self.e
         if e.stage < 3 or "shard_params" not in e._symm or not self.use_fused_gather:
             return False
-        rc = self.L.bz_pull_allgather(self._ptrs_for(e.shard_params), self._unit_segs[ui].data_ptr(),
-                                      len(e.layout.units[ui].params), e._unit_pbuf[ui].data_ptr(), e.rank,
-                                      e.world_size, self.rs_ctas, _lib.stream())
+        fn = self.L.bz_pull_allgather_v2 if self.pull_version == 2 else self.L.bz_pull_allgather
+        rc = fn(self._ptrs_for(e.shard_params), self._unit_segs[ui].data_ptr(),
+                len(e.layout.units[ui].params), e._unit_pbuf[ui].data_ptr(), e.rank,
+                e.world_size, self.rs_ctas, _lib.stream())
         _lib.check(rc, "pull_allgather")
         return True
 

@@ -169,6 +169,9 @@ int bz_fused_reduce_scatter_mc(void* const* grad_ptrs, void* const* signal_ptrs,
 /* ---- pull all-gather of a unit's rows from every peer's shard (ZeRO-3, X2) ---------- */
 int bz_pull_allgather(void* const* shard_param_ptrs, const void* segs, int nseg, void* dst_unit, int rank, int ws,
                       int ctas, void* stream);
+/* v2 (opt-in): walks the vector index and unrolls over the peers — no integer division per vector. */
+int bz_pull_allgather_v2(void* const* shard_param_ptrs, const void* segs, int nseg, void* dst_unit, int rank, int ws,
+                         int ctas, void* stream);
 
 /* ---- K6: causal flash attention forward (head_dim 128, GQA) on tcgen05 -----------
  * qkv: fused [B*S, (Hq+2*Hkv)*128] bf16 with RoPE applied; out: [B*S, Hq*128] bf16;

@@ -158,10 +158,13 @@ def main():
     torch.cuda.synchronize(); dist.barrier()
     ms = timeit(lambda: bz.check(L.bz_pull_allgather(sbuf.ptr_array(), segs.data_ptr(), 1, dst.data_ptr(), rank, ws,
                                                     128, bz.stream()), "pull"))
+    ms_v2 = timeit(lambda: bz.check(L.bz_pull_allgather_v2(sbuf.ptr_array(), segs.data_ptr(), 1, dst.data_ptr(), rank, ws,
+                                                           128, bz.stream()), "pull_v2")) if hasattr(L, "bz_pull_allgather_v2") else None
     ms_nccl = timeit(lambda: dist.all_gather_into_tensor(dst, sbuf.tensor(torch.bfloat16, n // ws)))
     target = remote / (NVLINK_GBS * 1e9) * 1e3
     res["pull_allgather"] = {"ms": ms, "achieved_gbs": remote / ms / 1e6, "target_ms": target,
-                             "fraction_of_roofline": target / ms, "nccl_allgather_ms": ms_nccl}
+                             "fraction_of_roofline": target / ms, "nccl_allgather_ms": ms_nccl,
+                             "v2_ms": ms_v2, "v2_fraction_of_roofline": (target / ms_v2) if ms_v2 else None}
     if rank == 0:
         os.makedirs(ROOT / "gpurun_out", exist_ok=True)
         json.dump(res, open(ROOT / "gpurun_out" / f"fused_roofline_n{ws}.json", "w"), indent=1)

@@ -12,6 +12,7 @@ if [ "${1:-single}" = "single" ]; then
   TMO=600 run gpt2_ops   python -m pytest tests/test_gpt2_ops.py -m gpu -q --runxfail
   TMO=600 run flash_v3   python -m pytest tests/test_attention.py -m gpu -q --runxfail -k v3
   TMO=900 run ag_dgrad   python -m pytest tests/test_ag_gemm_dgrad.py -m gpu -q --runxfail
+  TMO=600 run pull_v2    python -m pytest tests/test_fused_comm.py -m gpu -q --runxfail -k pull_allgather_v2
   TMO=600 run nvme_gpu   python -m pytest tests/test_nvme_offload.py -m gpu -q --runxfail
   TMO=600 run adam_overlap python -m pytest tests/test_native_llama.py -m gpu -q --runxfail -k overlap
   TMO=900 run bench_n1   python bench.py --steps 6 --warmup 3
@@ -28,6 +29,7 @@ else
   # followed by two bench runs that never finished ("Tried and backed out")
   TMO=600 run bench_default   $TR --master-port 29601 bench.py --gpus $N --steps 8 --warmup 3
   TMO=600 run bench_nccl      $TR --master-port 29602 bench.py --gpus $N --steps 4 --warmup 3 --comm nccl --skip-e2e
+  B200ZERO_PULL_AG=2 TMO=600 run bench_pull_v2 $TR --master-port 29607 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e
   B200ZERO_TEST_AG_DGRAD=1 TMO=600 run ag_dgrad_engine python -m pytest tests/test_fused_comm.py -m gpu -q -k dgrad
   B200ZERO_AG_DGRAD=1 TMO=600 run bench_ag_dgrad $TR --master-port 29606 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e
   B200ZERO_TEST_NVLS=1 TMO=600 run nvls_test python -m pytest tests/test_fused_comm.py -m gpu -q -k nvls

@@ -253,3 +253,53 @@ def test_module_path_fused_matches_nccl(stage):
     for out in run_ranks_nccl(_module_fused_vs_nccl_rank, world, (stage,)):
         assert out["fused"][0] == pytest.approx(out["nccl"][0], rel=5e-3)
         assert torch.allclose(out["fused"][1], out["nccl"][1], rtol=3e-2, atol=3e-3)
+
+
+_PULL_V2_CHECK = r"""
+import ctypes as C, sys, torch
+sys.path.insert(0, %r)
+from distributed_llm_training_gpu_manager_b200.ops import lib as bz
+from distributed_llm_training_gpu_manager_b200.parallel.fused import segment_table
+L = bz.load(required=True)
+torch.manual_seed(0)
+for W in (1, 2, 4, 8):
+    # two partitioned tensors and one replicated one inside a unit buffer
+    rows = [(64 * W, 128), (16 * W, 4096)]
+    recs, fo, so = [], 0, 0
+    for r_, c_ in rows:
+        recs.append((fo, r_ * c_, so, True)); fo += r_ * c_; so += r_ * c_ // W
+    recs.append((fo, 4096, so, False)); fo += 4096; so += 4096
+    unit_numel, shard_numel = fo, so
+    segs = segment_table(recs, "cuda")
+    shards = [torch.randn(shard_numel, device="cuda").bfloat16() for _ in range(W)]
+    ptrs = (C.c_void_p * W)(*[s.data_ptr() for s in shards])
+    for rank in range(W):
+        outs = []
+        for fn in (L.bz_pull_allgather, L.bz_pull_allgather_v2):
+            dst = torch.full((unit_numel,), float("nan"), device="cuda", dtype=torch.bfloat16)
+            bz.check(fn(ptrs, segs.data_ptr(), len(recs), dst.data_ptr(), rank, W, 16, bz.stream()), "pull")
+            torch.cuda.synchronize()
+            outs.append(dst)
+        assert torch.equal(outs[0], outs[1]), ("v2 differs from v1", W, rank)
+        for (f0, n, s0, part) in recs:
+            if part:
+                for p in range(W):
+                    assert torch.equal(outs[1][f0 + p * (n // W): f0 + (p + 1) * (n // W)], shards[p][s0:s0 + n // W])
+            else:
+                assert torch.equal(outs[1][f0:f0 + n], shards[rank][s0:s0 + n])
+print("PULL_V2_OK")
+"""
+
+
+@pytest.mark.xfail(strict=False, reason="division-free pull all-gather written after this round's GPU budget was spent")
+def test_pull_allgather_v2_matches_v1_emulated():
+    """Pure copy kernel without cross-rank waits: ranks are emulated on one GPU; v2 must reproduce v1 byte for byte.
+    Child process: not yet validated on hardware."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = str(Path(__file__).resolve().parent.parent)
+    res = subprocess.run([sys.executable, "-c", _PULL_V2_CHECK % root], capture_output=True, text=True, timeout=300,
+                         env=dict(os.environ))
+    assert "PULL_V2_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
