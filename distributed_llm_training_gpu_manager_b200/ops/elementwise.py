@@ -37,12 +37,13 @@ _lib.register("bz_rmsnorm_bwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.vp
                                               _lib.i32, _lib.vp, _lib.i32, _lib.i32, _lib.f32, _lib.vp])
 
 
-_lib.register("bz_swiglu_fwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.i64, _lib.i32, _lib.vp])
-_lib.register("bz_swiglu_bwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.i64, _lib.i32, _lib.vp])
+_lib.register("bz_swiglu_fwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.i64, _lib.i32, _lib.i32, _lib.vp])
+_lib.register("bz_swiglu_bwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.i64, _lib.i32, _lib.i32, _lib.vp])
 
 
 def _swiglu_version() -> int:
-    """2 = the division-free SwiGLU kernels of csrc/elementwise_v2.cu (opt-in until validated on hardware)."""
+    """2 = the division-free SwiGLU kernels of csrc/elementwise_v2.cu (bit-identical to v1), 3 = the same with
+    rcp.approx in the sigmoid (opt-in until validated on hardware)."""
     import os
     return int(os.environ.get("B200ZERO_SWIGLU", "1"))
 
@@ -178,8 +179,11 @@ def swiglu_fwd(gu: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
         return r
     out = out if out is not None else torch.empty((T, F), dtype=gu.dtype, device=gu.device)
     L = _lib.load()
-    fn = L.bz_swiglu_fwd_v2 if _swiglu_version() == 2 else L.bz_swiglu_fwd
-    _lib.check(fn(gu.data_ptr(), out.data_ptr(), T, F, _lib.stream()), "swiglu_fwd")
+    ver = _swiglu_version()
+    if ver >= 2:
+        _lib.check(L.bz_swiglu_fwd_v2(gu.data_ptr(), out.data_ptr(), T, F, int(ver == 3), _lib.stream()), "swiglu_fwd")
+    else:
+        _lib.check(L.bz_swiglu_fwd(gu.data_ptr(), out.data_ptr(), T, F, _lib.stream()), "swiglu_fwd")
     return out
 
 
@@ -196,8 +200,12 @@ def swiglu_bwd(gu: torch.Tensor, dact: torch.Tensor, out: Optional[torch.Tensor]
         return r
     out = out if out is not None else torch.empty_like(gu)
     L = _lib.load()
-    fn = L.bz_swiglu_bwd_v2 if _swiglu_version() == 2 else L.bz_swiglu_bwd
-    _lib.check(fn(gu.data_ptr(), dact.data_ptr(), out.data_ptr(), T, F, _lib.stream()), "swiglu_bwd")
+    ver = _swiglu_version()
+    if ver >= 2:
+        _lib.check(L.bz_swiglu_bwd_v2(gu.data_ptr(), dact.data_ptr(), out.data_ptr(), T, F, int(ver == 3), _lib.stream()),
+                   "swiglu_bwd")
+    else:
+        _lib.check(L.bz_swiglu_bwd(gu.data_ptr(), dact.data_ptr(), out.data_ptr(), T, F, _lib.stream()), "swiglu_bwd")
     return out
 
 

@@ -223,9 +223,9 @@ int bz_rmsnorm_bwd_v2(const void* x, const void* w, const float* rstd, const voi
                       void* stream);
 
 /* ---- K8, v2 (opt-in): SwiGLU forward / backward indexed by (row, vector) — no 64-bit integer division per vector
- * — with the correctly rounded reciprocal; same contracts and bit-identical results. */
-int bz_swiglu_fwd_v2(const void* gate_up, void* act, long long T, int F, void* stream);
-int bz_swiglu_bwd_v2(const void* gate_up, const void* dact, void* dgate_up, long long T, int F, void* stream);
+ * — with the correctly rounded reciprocal (bit-identical to v1) or, fast != 0, rcp.approx (2 ulp before bf16 rounding). */
+int bz_swiglu_fwd_v2(const void* gate_up, void* act, long long T, int F, int fast, void* stream);
+int bz_swiglu_bwd_v2(const void* gate_up, const void* dact, void* dgate_up, long long T, int F, int fast, void* stream);
 
 /* ---- GPT-2 family element-wise ops (csrc/gpt2_ops.cu) ----------
  * LayerNorm: y = (x - mean) * rstd * w + b over rows of width D (D % 8 == 0, D <= 16384); mean / rstd are

@@ -212,9 +212,13 @@ for T, F_ in ((64, 512), (300, 6400), (1000, 14336), (8192, 14336)):
     torch.cuda.synchronize()
     assert torch.equal(outs[1][0], outs[2][0]), ("swiglu fwd", T, F_)
     assert torch.equal(outs[1][1], outs[2][1]), ("swiglu bwd", T, F_)
+    os.environ["B200ZERO_SWIGLU"] = "3"                      # rcp.approx: within a bf16 ulp of v1
+    f3, b3 = E.swiglu_fwd(gu), E.swiglu_bwd(gu, da)
+    assert torch.allclose(f3.float(), outs[1][0].float(), rtol=8e-3, atol=1e-3), ("swiglu fwd fast", T, F_)
+    assert torch.allclose(b3.float(), outs[1][1].float(), rtol=8e-3, atol=1e-3), ("swiglu bwd fast", T, F_)
 T, F_ = 8192, 14336
 gu = torch.randn(T, 2 * F_, device="cuda").bfloat16(); da = torch.randn(T, F_, device="cuda").bfloat16()
-for ver in (1, 2):
+for ver in (1, 2, 3):
     os.environ["B200ZERO_SWIGLU"] = str(ver)
     for name, fn in (("swiglu_fwd", lambda: E.swiglu_fwd(gu)), ("swiglu_bwd", lambda: E.swiglu_bwd(gu, da))):
         ts = []
