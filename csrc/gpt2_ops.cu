@@ -191,17 +191,18 @@ __device__ __forceinline__ float gelu_tanh_grad(float v) {
 
 __global__ void __launch_bounds__(G2_THREADS)
 bias_gelu_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ b,
-                     __nv_bfloat16* __restrict__ y, long long T, int F) {
+                     __nv_bfloat16* __restrict__ y, int T, int F) {
   const int nvec = F >> 3;
-  const long long total = T * nvec;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int vc = (int)(i % nvec);
-    float xv[8], bv[8], o[8];
-    g2_load8(x + i * 8, xv);
-    g2_load8(b + vc * 8, bv);
+  for (int row = blockIdx.x; row < T; row += gridDim.x) {     // (row, vector) indexing: no integer division per vector
+    const size_t base = (size_t)row * F;
+    for (int vc = threadIdx.x; vc < nvec; vc += G2_THREADS) {
+      float xv[8], bv[8], o[8];
+      g2_load8(x + base + vc * 8, xv);
+      g2_load8(b + vc * 8, bv);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) o[e] = gelu_tanh(xv[e] + bv[e]);
-    g2_store8(y + i * 8, o);
+      for (int e = 0; e < 8; ++e) o[e] = gelu_tanh(xv[e] + bv[e]);
+      g2_store8(y + base + vc * 8, o);
+    }
   }
 }
 
@@ -312,13 +313,11 @@ extern "C" int bz_layernorm_bwd(const void* x, const void* w, const float* mean,
 
 extern "C" int bz_bias_gelu_fwd(const void* x, const void* bias, void* y, long long T, int F, void* stream) {
   BZ_REQUIRE(F % 8 == 0 && F > 0, "bias_gelu_fwd: F=%d must be a positive multiple of 8", F);
+  BZ_REQUIRE(T < (1LL << 31), "bias_gelu_fwd: T too large");
   if (T <= 0) return 0;
-  const long long total = T * (F >> 3);
-  const int sms = device_sm_count();
-  long long blocks = (total + G2_THREADS - 1) / G2_THREADS;
-  if (blocks > (long long)sms * 16) blocks = (long long)sms * 16;
-  bias_gelu_fwd_kernel<<<(int)blocks, G2_THREADS, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, T, F);
+  const int grid = (int)min((long long)device_sm_count() * 8, T);
+  bias_gelu_fwd_kernel<<<grid, G2_THREADS, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, (int)T, F);
   BZ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
