@@ -1,12 +1,13 @@
 #!/usr/bin/env bash
 # First GPU call of the next session: run everything that was written after the round-1 GPU budget was spent.
 # One box, 1 GPU unless noted; every step has its own time limit; results land in gpurun_out/.
-#   gpurun --timeout 1500 -- 'bash scripts/validate_pending.sh'            (1 GPU part)
-#   gpurun --gpus 2 --timeout 1200 -- 'bash scripts/validate_pending.sh multi'   (NVLS K1, bench supervisor, N=2)
+#   gpurun --timeout 1200 -- 'bash scripts/validate_pending.sh tests'          (1 GPU: child-process kernel tests, ~6 min)
+#   gpurun --timeout 1500 -- 'bash scripts/validate_pending.sh bench'          (1 GPU: bench.py per opt-in, ~18 min)
+#   gpurun --gpus 2 --timeout 1200 -- 'bash scripts/validate_pending.sh multi' (NVLS K1, dgrad, supervisor, N=2)
 set -u
 mkdir -p gpurun_out
 run() { local name=$1; shift; echo "=== $name"; timeout "${TMO:-600}" "$@" > "gpurun_out/pending_$name.log" 2>&1; echo "rc=$? ($name)"; tail -4 "gpurun_out/pending_$name.log"; }
-if [ "${1:-single}" = "single" ]; then
+if [ "${1:-tests}" = "tests" ]; then
   # the child-process tests report xfail/xpass; --runxfail turns a failure into a visible failure
   TMO=600 run rmsnorm_v2 python -m pytest tests/test_elementwise.py -m gpu -q --runxfail -k v2
   TMO=600 run gpt2_ops   python -m pytest tests/test_gpt2_ops.py -m gpu -q --runxfail
@@ -15,12 +16,14 @@ if [ "${1:-single}" = "single" ]; then
   TMO=600 run pull_v2    python -m pytest tests/test_fused_comm.py -m gpu -q --runxfail -k pull_allgather_v2
   TMO=600 run nvme_gpu   python -m pytest tests/test_nvme_offload.py -m gpu -q --runxfail
   TMO=600 run adam_overlap python -m pytest tests/test_native_llama.py -m gpu -q --runxfail -k overlap
+elif [ "$1" = "bench" ]; then
   TMO=900 run bench_n1   python bench.py --steps 6 --warmup 3
   B200ZERO_ADAM_OVERLAP=1 TMO=900 run bench_n1_adam_overlap python bench.py --steps 6 --warmup 3 --skip-halt
   B200ZERO_FLASH_BWD=3  TMO=900 run bench_n1_flashbwd3 python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_RMSNORM=2 B200ZERO_SWIGLU=2 TMO=900 run bench_n1_elementwise2 python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_FLASH_FWD=3  TMO=900 run bench_n1_flash3   python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
   B200ZERO_FLASH_FWD=34 TMO=900 run bench_n1_flash34  python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt
+  B200ZERO_FLASH_FWD=3 B200ZERO_FLASH_BWD=3 B200ZERO_RMSNORM=2 B200ZERO_SWIGLU=3 B200ZERO_ADAM_OVERLAP=1 TMO=900 run bench_n1_all_optins python bench.py --steps 6 --warmup 3 --skip-halt
   B200ZERO_GPT2_NATIVE_OPS=1 TMO=600 run gpt2xl_native_ops python bench.py --steps 4 --warmup 3 --skip-e2e --skip-halt --model gpt2-xl --zero-stage 2 --seq-len 1024 --micro-batch 8 --engine module
 else
   N=$(nvidia-smi -L | wc -l)
