@@ -5,7 +5,6 @@ direction per GPU); achieved fraction = target / measured. Writes gpurun_out/fus
 
     python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 scripts/bench_fused_multigpu.py
 """
-import ctypes as C
 import json
 import os
 import sys

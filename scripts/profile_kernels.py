@@ -5,7 +5,7 @@ import ctypes as C, sys
 from pathlib import Path
 import torch
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
-from distributed_llm_training_gpu_manager_b200.ops import gemm as G, lib as bz, elementwise as E, optim as O
+from distributed_llm_training_gpu_manager_b200.ops import gemm as G, lib as bz, elementwise as E
 from distributed_llm_training_gpu_manager_b200.ops.flash import flash_fwd, flash_bwd
 from distributed_llm_training_gpu_manager_b200.ops.ag_gemm import ag_linear_fwd, ptr_array
 from distributed_llm_training_gpu_manager_b200.parallel.fused import segment_table

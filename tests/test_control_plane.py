@@ -12,8 +12,7 @@ from hypothesis import given, settings, strategies as st
 
 from distributed_llm_training_gpu_manager_b200.ai_engine import (DeepSpeedConfig, DeepSpeedLauncher, GPUManager,
                                                                   HaltAction, HaltPolicy, LossSpikeMonitor,
-                                                                  MonitorConfig, OffloadDevice, TrainingMetrics,
-                                                                  ZeROStage)
+                                                                  MonitorConfig, OffloadDevice, TrainingMetrics)
 from distributed_llm_training_gpu_manager_b200.ai_engine.loss_monitor import RollingStats
 
 REF = Path("/root/reference/ai_engine")
