@@ -550,7 +550,8 @@ class ZeroEngine:
             if self.world_size > 1:
                 repl = st[3].clone()
                 st[3] = 0
-                dist.all_reduce(st)           # Σ‖g‖² (X6), overflow flag (X5), mean loss (X8) in one message
+                if self.fused is None or not self.fused.allreduce_stats(st):
+                    dist.all_reduce(st)       # Σ‖g‖² (X6), overflow flag (X5), mean loss (X8) in one message
                 st[3] = repl
             self._sumsq[0] = st[0] + st[3]
             self._flag[0] = (st[1] > 0).int()

@@ -68,6 +68,7 @@ _SIGNATURES = {
                                          C.c_uint, i32, i32, i32, i32, i32, vp]),
     "bz_pull_allgather": (i32, [C.POINTER(vp), vp, i32, vp, i32, i32, i32, vp]),
     "bz_pull_allgather_v2": (i32, [C.POINTER(vp), vp, i32, vp, i32, i32, i32, vp]),
+    "bz_peer_allreduce4": (i32, [C.POINTER(vp), vp, C.c_uint, i32, i32, i32, vp]),
 }
 
 

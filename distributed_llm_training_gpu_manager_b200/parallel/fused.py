@@ -21,7 +21,7 @@ import torch
 from ..ops import lib as _lib
 from .symm import SymmetricBuffer, nvls_buffer_or_none
 
-RS_CHANNEL, ADAM_CHANNEL = 0, 1
+RS_CHANNEL, ADAM_CHANNEL, STATS_CHANNEL = 0, 1, 2
 
 
 def segment_table(records: List[tuple], device) -> torch.Tensor:
@@ -51,7 +51,9 @@ class FusedComm:
         self.workspace = torch.zeros(self.L.bz_fused_comm_workspace_bytes() // 4, dtype=torch.float32, device=dev)
         self.sumsq_part = torch.zeros(1, dtype=torch.float32, device=dev)
         self.sumsq_repl = torch.zeros(1, dtype=torch.float32, device=dev)
-        self.epoch = {RS_CHANNEL: 0, ADAM_CHANNEL: 0}
+        self.epoch = {RS_CHANNEL: 0, ADAM_CHANNEL: 0, STATS_CHANNEL: 0}
+        # X5/X6/X8 without NCCL (opt-in): the step's 4-float control vector is exchanged through the signal pads
+        self.peer_stats = os.environ.get("B200ZERO_STATS_PEER", "0") == "1"
         self._sig_ptrs = self.signal.ptr_array()
         L = engine.layout
         # per-unit segment tables (offsets relative to the unit's buffer)
@@ -118,6 +120,19 @@ class FusedComm:
             rc = self.L.bz_fused_reduce_scatter(self._ptrs_for(gb), self._sig_ptrs, *tail)
         _lib.check(rc, "fused_reduce_scatter")
         _lib.add_launches(1)
+        return True
+
+    # -- control exchange ------------------------------------------------------------------------
+    def allreduce_stats(self, st: torch.Tensor) -> bool:
+        """Sum the engine's 4-float stats vector over all ranks in place (rank-ordered, bit-identical everywhere).
+        Returns False when the peer path is off (the caller then uses the NCCL all-reduce)."""
+        if not self.peer_stats:
+            return False
+        assert st.numel() == 4 and st.dtype == torch.float32
+        self.epoch[STATS_CHANNEL] += 1
+        rc = self.L.bz_peer_allreduce4(self._sig_ptrs, st.data_ptr(), self.epoch[STATS_CHANNEL], STATS_CHANNEL,
+                                       self.e.rank, self.e.world_size, _lib.stream())
+        _lib.check(rc, "peer_allreduce4")
         return True
 
     # -- ZeRO-3 gather -------------------------------------------------------------------------

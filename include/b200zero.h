@@ -157,6 +157,12 @@ int bz_fused_adam_push(void* const* param_ptrs, void* const* signal_ptrs, const 
                        int channel, int rank, int ws, int push, int use_barrier, int zero_grads, int ctas,
                        void* stream);
 
+/* ---- X5/X6/X8 without NCCL (opt-in): sum four device floats over all ranks through the signal pads
+ * (16-byte peer stores + epoch flag, rank-ordered sum: bit-identical on every rank). One call per step on every
+ * rank with the same growing epoch and a channel of its own. */
+int bz_peer_allreduce4(void* const* signal_ptrs, float* vals4, unsigned int epoch, int channel, int rank, int ws,
+                       void* stream);
+
 /* ---- K1, NVLS flavour (opt-in): the gradient buffer is additionally mapped through an NVSwitch
  * multicast object (grad_mc = multicast VA of the buffer whose per-rank VAs are in grad_ptrs).
  * Partitioned tensors are summed inside the switch (multimem.ld_reduce); replicated tensors,

@@ -32,7 +32,8 @@ else
   # followed by two bench runs that never finished ("Tried and backed out")
   TMO=600 run bench_default   $TR --master-port 29601 bench.py --gpus $N --steps 8 --warmup 3
   TMO=600 run bench_nccl      $TR --master-port 29602 bench.py --gpus $N --steps 4 --warmup 3 --comm nccl --skip-e2e
-  B200ZERO_PULL_AG=2 TMO=600 run bench_pull_v2 $TR --master-port 29607 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e
+  B200ZERO_TEST_UNVALIDATED=1 TMO=600 run peer_stats_pull_v2 python -m pytest tests/test_fused_comm.py -m gpu -q -k peer_stats
+  B200ZERO_PULL_AG=2 B200ZERO_STATS_PEER=1 TMO=600 run bench_pull_v2_peer_stats $TR --master-port 29607 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e
   B200ZERO_TEST_AG_DGRAD=1 TMO=600 run ag_dgrad_engine python -m pytest tests/test_fused_comm.py -m gpu -q -k dgrad
   B200ZERO_AG_DGRAD=1 TMO=600 run bench_ag_dgrad $TR --master-port 29606 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e
   B200ZERO_TEST_NVLS=1 TMO=600 run nvls_test python -m pytest tests/test_fused_comm.py -m gpu -q -k nvls

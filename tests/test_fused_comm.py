@@ -135,11 +135,13 @@ def test_adam_push_and_pull_allgather_emulated():
             assert torch.equal(dst[fo:fo + n], params[r][fo:fo + n]) or not part
 
 
-def _fused_vs_nccl_rank(rank, world, stage, gas=1, nvls=False, ag_dgrad=False):
+def _fused_vs_nccl_rank(rank, world, stage, gas=1, nvls=False, ag_dgrad=False, peer_stats=False, pull_v2=False):
     import os
     import torch.distributed as dist
     os.environ["B200ZERO_NVLS"] = "1" if nvls else "0"
     os.environ["B200ZERO_AG_DGRAD"] = "1" if ag_dgrad else "0"
+    os.environ["B200ZERO_STATS_PEER"] = "1" if peer_stats else "0"
+    os.environ["B200ZERO_PULL_AG"] = "2" if pull_v2 else "1"
     from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
     from distributed_llm_training_gpu_manager_b200.models import get_config
     from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
@@ -184,6 +186,22 @@ def test_nvls_multimem_path_matches_nccl(stage):
         pytest.skip("no NVLS multicast support on this box")
     for out in outs:
         assert out["nvls_launches"] > 0
+        assert out["fused"][0] == pytest.approx(out["nccl"][0], rel=2e-3)
+        assert out["fused"][1] == pytest.approx(out["nccl"][1], rel=2e-2)
+        assert torch.allclose(out["fused"][2], out["nccl"][2], rtol=2e-2, atol=2e-3)
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("stage", [2, 3])
+def test_peer_stats_and_pull_v2_in_engine_match_nccl(stage):
+    """B200ZERO_STATS_PEER=1 (the step's control vector through the signal pads instead of a 16-byte NCCL
+    all-reduce) and B200ZERO_PULL_AG=2. Opt-in (B200ZERO_TEST_UNVALIDATED=1) until they have run on hardware."""
+    import os
+    if os.environ.get("B200ZERO_TEST_UNVALIDATED", "0") != "1":
+        pytest.skip("not yet validated on GPUs: set B200ZERO_TEST_UNVALIDATED=1")
+    from dist_utils import run_ranks_nccl
+    world = min(torch.cuda.device_count(), 4)
+    for out in run_ranks_nccl(_fused_vs_nccl_rank, world, (stage, 1, False, False, True, True), timeout=240):
         assert out["fused"][0] == pytest.approx(out["nccl"][0], rel=2e-3)
         assert out["fused"][1] == pytest.approx(out["nccl"][1], rel=2e-2)
         assert torch.allclose(out["fused"][2], out["nccl"][2], rtol=2e-2, atol=2e-3)
