@@ -16,15 +16,17 @@ import time
 import pytest
 
 UNITS, STEPS = 5, 4
-RS, ADAM = 0, 1
+RS, ADAM, STATS = 0, 1, 2
 
 
 class World:
-    def __init__(self, ws, k1_phase1=True, k3_phase2=True, seed=0):
+    def __init__(self, ws, k1_phase1=True, k3_phase2=True, seed=0, stats_bufs=2):
         self.ws = ws
-        self.k1_phase1, self.k3_phase2 = k1_phase1, k3_phase2
+        self.k1_phase1, self.k3_phase2, self.stats_bufs = k1_phase1, k3_phase2, stats_bufs
+        # payload[r][buf][src]: the control vector src published to r for one exchange
+        self.payload = [[[None] * ws for _ in range(2)] for _ in range(ws)]
         # signal[r][(channel, phase)][src] = last epoch announced by src to r
-        self.signal = [{(c, p): [0] * ws for c in (RS, ADAM) for p in (0, 1)} for _ in range(ws)]
+        self.signal = [{(c, p): [0] * ws for c in (RS, ADAM, STATS) for p in (0, 1)} for _ in range(ws)]
         self.grad_slot = [[None, None] for _ in range(ws)]            # two pooled gradient buffers per rank
         self.params = [[None] * ws for _ in range(ws)]                # params[r][owner] = tag of owner's rows as seen by r
         self.errors = []
@@ -67,6 +69,24 @@ def k3(w, r, step, epoch):
         w.params[dst][r] = step
     if w.k3_phase2:
         w.signal_all_and_wait(r, ADAM, 1, epoch)
+
+
+def stats_exchange(w, r, step, epoch):
+    """bz_peer_allreduce4: payload into every peer's pad, flag, wait for all flags, read all payloads."""
+    buf = epoch % w.stats_bufs
+    for dst in range(w.ws):
+        w.payload[dst][buf][r] = step
+        w.nap(r, 0.2)
+        w.signal[dst][(STATS, 0)][r] = epoch
+    mine = w.signal[r][(STATS, 0)]
+    while any(mine[src] - epoch < 0 for src in range(w.ws)):
+        if time.time() > w.deadline:
+            raise TimeoutError(f"rank {r} stuck in the stats exchange, epoch {epoch}: {mine}")
+        time.sleep(0)
+    w.nap(r, 2.0)                                                    # adversarial: slow reader
+    for src in range(w.ws):
+        if w.payload[r][buf][src] != step:
+            w.fail(f"rank {r} summed rank {src}'s vector of step {w.payload[r][buf][src]} in step {step}")
 
 
 def rank_main(w, r):
@@ -115,6 +135,7 @@ def rank_main(w, r):
                 rs_epoch += 1
                 comm_q.put((step, unit, rs_epoch))                    # ... then K1 is enqueued behind them
             comm_done.wait()                                          # main stream waits for the comm stream
+            stats_exchange(w, r, step, step)
             adam_epoch += 1
             k3(w, r, step, adam_epoch)
     except Exception as exc:  # noqa: BLE001
@@ -158,6 +179,43 @@ def test_model_has_teeth_without_k3_barrier():
     for seed in range(6):
         w = run_world(4, k3_phase2=False, seed=seed)
         if any("forward" in e for e in w.errors):
+            caught = True
+            break
+    assert caught
+
+
+def run_exchange_only(ws, stats_bufs, seed, steps=8):
+    """Back-to-back bz_peer_allreduce4 calls with nothing else between them (the kernel's own contract, without
+    the K3 barrier that happens to follow it in the engine)."""
+    w = World(ws, seed=seed, stats_bufs=stats_bufs)
+
+    def rank(r):
+        try:
+            for step in range(1, steps + 1):
+                stats_exchange(w, r, step, step)
+        except Exception as exc:  # noqa: BLE001
+            w.fail(f"rank {r}: {exc!r}")
+    threads = [threading.Thread(target=rank, args=(r,), daemon=True) for r in range(ws)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(60)
+    assert not any(t.is_alive() for t in threads), "model deadlocked"
+    return w
+
+
+@pytest.mark.parametrize("ws", [2, 4, 8])
+def test_stats_exchange_is_safe_back_to_back(ws):
+    for seed in range(3):
+        assert run_exchange_only(ws, 2, seed).errors == []
+
+
+def test_model_has_teeth_without_stats_double_buffer():
+    """One payload buffer is not enough: a fast rank's next vector lands before a slow rank has read this one."""
+    caught = False
+    for seed in range(6):
+        w = run_exchange_only(4, 1, seed)
+        if any("summed" in e for e in w.errors):
             caught = True
             break
     assert caught
