@@ -41,4 +41,5 @@ else
   TMO=600 run bench_after_nvls $TR --master-port 29604 bench.py --gpus $N --steps 4 --warmup 3 --skip-e2e
   B200ZERO_BENCH_NVLS=1 TMO=300 run roofline $TR --master-port 29605 scripts/bench_fused_multigpu.py
 fi
+grep -h "_OK" gpurun_out/*_check.log 2>/dev/null | cut -c1-300     # timing lines of the child-process kernel checks
 grep -h "^{" gpurun_out/pending_bench_*.log 2>/dev/null | cut -c1-400
