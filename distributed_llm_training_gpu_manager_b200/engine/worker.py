@@ -44,6 +44,8 @@ def main(argv=None) -> int:
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--window", type=int, default=100)
     ap.add_argument("--seed", type=int, default=1234)
+    ap.add_argument("--data", default=None, help="flat binary token file (uint16/uint32); default: synthetic tokens")
+    ap.add_argument("--data_dtype", default="auto", help="auto | uint16 | uint32 | int32 | int64")
     ns = ap.parse_args(argv)
     if os.environ.get("B200ZERO_HANG_DUMP"):  # debugging aid: dump all stacks and exit after N seconds
         import faulthandler
@@ -67,7 +69,12 @@ def main(argv=None) -> int:
     else:
         from .zero import ZeroEngine
         engine = ZeroEngine(build_torch_model(mcfg), ecfg, device=device, comm=ns.comm)
-    batches = synthetic_batches(mcfg.vocab_size, ecfg.micro_batch, seq, device, rank, world, seed=ns.seed)
+    if ns.data:
+        from .data import token_batches
+        batches = token_batches(ns.data, ecfg.micro_batch, seq, device, rank, world, seed=ns.seed,
+                                dtype=ns.data_dtype, vocab_size=mcfg.vocab_size)
+    else:
+        batches = synthetic_batches(mcfg.vocab_size, ecfg.micro_batch, seq, device, rank, world, seed=ns.seed)
     tcfg = TrainerConfig(total_steps=ns.steps, save_dir=ns.save_dir, save_every=ns.save_every,
                          metrics_path=ns.metrics, monitor=MonitorConfig(window_size=ns.window), log_every=10)
     res = Trainer(engine, batches, tcfg).run()
