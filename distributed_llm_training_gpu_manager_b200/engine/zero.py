@@ -706,6 +706,40 @@ class ZeroEngine:
                 sd[spec.name] = self.param_view(spec.name).detach().clone().cpu()
         return sd
 
+    def load_full_params(self, named: Dict[str, torch.Tensor], strict: bool = True) -> List[str]:
+        """Initialise the model from full (unsharded) tensors by parameter name — e.g. a converted Hugging Face
+        checkpoint (``models/hf.py``) or the output of ``zero_to_fp32.py``. Every rank passes the same dict and keeps
+        its own rows; Adam moments and step counters are left untouched. Returns the names that were not supplied."""
+        self._join_adam()
+        missing = []
+        for u in self.layout.units:
+            for spec in u.params:
+                t = named.get(spec.name)
+                if t is None:
+                    missing.append(spec.name)
+                    continue
+                if tuple(t.shape) != tuple(spec.shape):
+                    raise ValueError(f"{spec.name}: expected shape {tuple(spec.shape)}, got {tuple(t.shape)}")
+                dst = self.master[spec.shard_offset:spec.shard_offset + spec.shard_numel]
+                dst.copy_(self._slice_rows(spec, t.detach().to(torch.float32)))
+        if strict and missing:
+            raise KeyError(f"parameters not supplied: {missing[:8]}{' ...' if len(missing) > 8 else ''}")
+        self.shard_params.copy_(self.master.to(self.device).to(self.compute_dtype))
+        if _dist_ready() and self.world_size > 1:
+            if self.on_cuda:
+                torch.cuda.synchronize(self.device)      # peers read this shard directly in the fused gather
+            dist.barrier()
+        if self.stage >= 3 and self.pooled_params:
+            self._resident = [False] * len(self.layout.units)
+            self._slot_owner = [None, None]
+            self._gather_unit(0)
+        else:
+            for ui in range(len(self.layout.units)):
+                self._gather_unit(ui)
+        if _dist_ready() and self.world_size > 1:
+            dist.barrier()
+        return missing
+
     def save_checkpoint(self, save_dir: str, tag: Optional[str] = None, client_state: Optional[Dict] = None,
                         async_write: bool = False):
         from .checkpoint import save_checkpoint

@@ -1,0 +1,62 @@
+"""Hugging Face Llama layout <-> ours. transformers' own LlamaForCausalLM (random tiny config, fp32, CPU) is an
+independent oracle for the model math: same logits from our nn.Module, same loss from the native executor."""
+import pytest
+import torch
+
+transformers = pytest.importorskip("transformers")
+
+
+def _tiny_hf(tie=False):
+    from transformers import LlamaConfig, LlamaForCausalLM
+    hc = LlamaConfig(vocab_size=1000, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                     num_attention_heads=2, num_key_value_heads=1, max_position_embeddings=256, rms_norm_eps=1e-5,
+                     rope_theta=500000.0, tie_word_embeddings=tie, attention_bias=False, mlp_bias=False)
+    torch.manual_seed(0)
+    return hc, LlamaForCausalLM(hc).float().eval()
+
+
+@pytest.mark.parametrize("tie", [False, True])
+def test_module_matches_transformers_logits(tie):
+    from distributed_llm_training_gpu_manager_b200.models import build_torch_model
+    from distributed_llm_training_gpu_manager_b200.models.hf import config_from_hf, from_hf_state_dict, to_hf_state_dict
+    hc, hf = _tiny_hf(tie)
+    cfg = config_from_hf(hc)
+    assert cfg.padded_vocab == 1024 and cfg.head_dim == 128 and cfg.n_kv_heads == 1
+    named = from_hf_state_dict(hf.state_dict(), cfg)
+    ours = build_torch_model(cfg).float().eval()
+    ours.load_state_dict(named, strict=not tie)
+    ids = torch.randint(0, 1000, (2, 64))
+    with torch.no_grad():
+        lh, lo = hf(input_ids=ids).logits, ours(ids)
+    assert (lh - lo[..., :1000]).abs().max().item() < 1e-4
+    back = to_hf_state_dict(named, cfg)
+    for k, v in hf.state_dict().items():
+        if k in back:
+            assert torch.equal(back[k], v.float()), k
+
+
+def test_native_engine_loads_hf_weights_and_matches_loss():
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.models.hf import config_from_hf, from_hf_state_dict
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+    hc, hf = _tiny_hf()
+    cfg = config_from_hf(hc)
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-4, warmup_steps=1,
+        wall_clock_breakdown=False))
+    eng = NativeLlamaEngine(cfg, ds, seq_len=64, device=torch.device("cpu"), seed=5)
+    assert eng.load_full_params(from_hf_state_dict(hf.state_dict(), cfg)) == []
+    ids = torch.randint(0, 1000, (2, 64))
+    labels = torch.randint(0, 1000, (2, 64))
+    with torch.no_grad():
+        ref = torch.nn.functional.cross_entropy(hf(input_ids=ids).logits.view(-1, 1000), labels.view(-1)).item()
+    loss = float(eng.forward(ids, labels))
+    # the padded vocabulary rows are zero: they add exp(0)·24 to every partition function, a known offset
+    with torch.no_grad():
+        z = hf(input_ids=ids).logits.view(-1, 1000)
+        lse_pad = torch.logsumexp(torch.cat([z, torch.zeros(z.shape[0], 24)], 1), 1)
+        ref_padded = (lse_pad - z.gather(1, labels.view(-1, 1)).squeeze(1)).mean().item()
+    assert loss == pytest.approx(ref_padded, rel=1e-4), (loss, ref, ref_padded)
+    with pytest.raises(ValueError):
+        eng.load_full_params({"embed.weight": torch.zeros(3, 3)}, strict=False)
