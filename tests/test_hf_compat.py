@@ -60,3 +60,51 @@ def test_native_engine_loads_hf_weights_and_matches_loss():
     assert loss == pytest.approx(ref_padded, rel=1e-4), (loss, ref, ref_padded)
     with pytest.raises(ValueError):
         eng.load_full_params({"embed.weight": torch.zeros(3, 3)}, strict=False)
+
+
+def test_native_backward_matches_transformers_autograd():
+    """Hand-written backward of the native executor (CPU restatements of the kernels) against autograd through
+    transformers' implementation: every gradient, with a vocabulary that needs no padding so the losses are equal."""
+    from transformers import LlamaConfig, LlamaForCausalLM
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.models.hf import config_from_hf, from_hf_state_dict
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+    hc = LlamaConfig(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                     num_attention_heads=2, num_key_value_heads=1, max_position_embeddings=256, rms_norm_eps=1e-5,
+                     rope_theta=500000.0, tie_word_embeddings=False, attention_bias=False, mlp_bias=False)
+    torch.manual_seed(1)
+    hf = LlamaForCausalLM(hc).float()
+    cfg = config_from_hf(hc)
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-4, warmup_steps=1,
+        gradient_clipping=0.0, wall_clock_breakdown=False))
+    eng = NativeLlamaEngine(cfg, ds, seq_len=64, device=torch.device("cpu"), seed=5)
+    eng.load_full_params(from_hf_state_dict(hf.state_dict(), cfg))
+    ids = torch.randint(0, 1024, (2, 64))
+    labels = torch.randint(0, 1024, (2, 64))
+    ref_loss = torch.nn.functional.cross_entropy(hf(input_ids=ids).logits.view(-1, 1024), labels.view(-1))
+    ref_loss.backward()
+    loss = eng.forward(ids, labels)
+    assert float(loss) == pytest.approx(ref_loss.item(), rel=1e-5)
+    eng.backward(loss)
+    sd = dict(hf.named_parameters())
+    g = lambda k: sd[k].grad  # noqa: E731
+
+    def close(ours, ref, name):
+        scale = ref.abs().max().item() + 1e-12
+        assert (ours.float() - ref).abs().max().item() / scale < 2e-4, name
+    close(eng.grad_view("embed.weight"), g("model.embed_tokens.weight"), "embed")
+    close(eng.grad_view("lm_head.weight"), g("lm_head.weight"), "lm_head")
+    close(eng.grad_view("final_norm.weight"), g("model.norm.weight"), "final_norm")
+    for i in range(2):
+        h, p = f"model.layers.{i}.", f"blocks.{i}."
+        close(eng.grad_view(p + "wqkv.weight"),
+              torch.cat([g(h + "self_attn.q_proj.weight"), g(h + "self_attn.k_proj.weight"),
+                         g(h + "self_attn.v_proj.weight")], 0), p + "wqkv")
+        close(eng.grad_view(p + "wo.weight"), g(h + "self_attn.o_proj.weight"), p + "wo")
+        close(eng.grad_view(p + "w_gate_up.weight"),
+              torch.cat([g(h + "mlp.gate_proj.weight"), g(h + "mlp.up_proj.weight")], 0), p + "w_gate_up")
+        close(eng.grad_view(p + "w_down.weight"), g(h + "mlp.down_proj.weight"), p + "w_down")
+        close(eng.grad_view(p + "attn_norm.weight"), g(h + "input_layernorm.weight"), p + "attn_norm")
+        close(eng.grad_view(p + "ffn_norm.weight"), g(h + "post_attention_layernorm.weight"), p + "ffn_norm")
