@@ -86,3 +86,30 @@ def to_hf_state_dict(named: Mapping[str, torch.Tensor], cfg: ModelConfig) -> Dic
         out[h + "mlp.up_proj.weight"] = gu[cfg.ffn:].clone()
         out[h + "mlp.down_proj.weight"] = named[p + "w_down.weight"].clone()
     return out
+
+
+# ------------------------------------------------------------------ GPT-2
+def gpt2_config_from_hf(hf_cfg) -> ModelConfig:
+    """``transformers.GPT2Config`` -> ``ModelConfig`` (GELU must be the tanh form, "gelu_new")."""
+    inner = hf_cfg.n_inner or 4 * hf_cfg.n_embd
+    return ModelConfig("gpt2", hf_cfg.vocab_size, hf_cfg.n_embd, hf_cfg.n_layer, hf_cfg.n_head, hf_cfg.n_head, inner,
+                       hf_cfg.n_positions, norm_eps=float(hf_cfg.layer_norm_epsilon), tie_embeddings=True)
+
+
+_GPT2_LINEAR = (("attn.c_attn", "attn_qkv"), ("attn.c_proj", "attn_proj"), ("mlp.c_fc", "mlp_fc"), ("mlp.c_proj", "mlp_proj"))
+
+
+def gpt2_from_hf_state_dict(sd: Mapping[str, torch.Tensor], cfg: ModelConfig) -> Dict[str, torch.Tensor]:
+    """GPT-2 in ``transformers`` stores its projections as ``Conv1D`` ([in, out]); ours are ``nn.Linear``
+    ([out, in]) — the conversion is a transpose. q | k | v are fused along the output dimension in both."""
+    g = lambda k: sd[k].detach().to(torch.float32).cpu()  # noqa: E731
+    out = {"wte.weight": _pad_vocab(g("transformer.wte.weight"), cfg.padded_vocab), "wpe.weight": g("transformer.wpe.weight"),
+           "ln_f.weight": g("transformer.ln_f.weight"), "ln_f.bias": g("transformer.ln_f.bias")}
+    for i in range(cfg.n_layers):
+        h, p = f"transformer.h.{i}.", f"blocks.{i}."
+        for ln in ("ln_1", "ln_2"):
+            out[p + ln + ".weight"], out[p + ln + ".bias"] = g(h + ln + ".weight"), g(h + ln + ".bias")
+        for theirs, ours in _GPT2_LINEAR:
+            out[p + ours + ".weight"] = g(h + theirs + ".weight").t().contiguous()
+            out[p + ours + ".bias"] = g(h + theirs + ".bias")
+    return out

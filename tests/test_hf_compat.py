@@ -108,3 +108,30 @@ def test_native_backward_matches_transformers_autograd():
         close(eng.grad_view(p + "w_down.weight"), g(h + "mlp.down_proj.weight"), p + "w_down")
         close(eng.grad_view(p + "attn_norm.weight"), g(h + "input_layernorm.weight"), p + "attn_norm")
         close(eng.grad_view(p + "ffn_norm.weight"), g(h + "post_attention_layernorm.weight"), p + "ffn_norm")
+
+
+def test_gpt2_module_matches_transformers():
+    from transformers import GPT2Config, GPT2LMHeadModel
+    from distributed_llm_training_gpu_manager_b200.models import build_torch_model
+    from distributed_llm_training_gpu_manager_b200.models.hf import gpt2_config_from_hf, gpt2_from_hf_state_dict
+    hc = GPT2Config(vocab_size=512, n_positions=128, n_embd=128, n_layer=2, n_head=4, activation_function="gelu_new",
+                    resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)
+    torch.manual_seed(0)
+    hf = GPT2LMHeadModel(hc).float().eval()
+    cfg = gpt2_config_from_hf(hc)
+    ours = build_torch_model(cfg).float().eval()
+    ours.load_state_dict(gpt2_from_hf_state_dict(hf.state_dict(), cfg), strict=True)
+    ids = torch.randint(0, 512, (2, 48))
+    with torch.no_grad():
+        lh, lo = hf(input_ids=ids).logits, ours(ids)
+    assert (lh - lo[..., :512]).abs().max().item() < 1e-4
+    # and the loss / gradients through both
+    hf.train(); ours.train()
+    labels = torch.randint(0, 512, (2, 48))
+    l_ref = torch.nn.functional.cross_entropy(hf(input_ids=ids).logits.view(-1, 512), labels.view(-1))
+    l_ref.backward()
+    l_ours = ours(ids, labels)
+    l_ours.backward()
+    assert l_ours.item() == pytest.approx(l_ref.item(), rel=1e-5)
+    ref_g = hf.transformer.h[0].mlp.c_fc.weight.grad.t()
+    assert torch.allclose(ours.blocks[0].mlp_fc.weight.grad, ref_g, rtol=1e-3, atol=1e-6)
