@@ -695,6 +695,11 @@ class ZeroEngine:
         _all_gather(out, local.contiguous())
         return out.view(spec.shape)
 
+    def full_state_dict(self) -> Dict[str, torch.Tensor]:
+        """Every parameter as a full fp32 tensor from the master copy, on the CPU (collective: all ranks call it;
+        all ranks receive it). Feed it to ``models.hf.to_hf_state_dict`` to leave for the transformers layout."""
+        return {spec.name: self.full_param(spec.name).cpu() for u in self.layout.units for spec in u.params}
+
     def module_state_dict(self) -> Dict[str, torch.Tensor]:
         """16-bit (compute dtype) weights by name, gathered (``stage3_gather_16bit_weights_on_model_save``)."""
         self._join_adam()

@@ -135,3 +135,30 @@ def test_gpt2_module_matches_transformers():
     assert l_ours.item() == pytest.approx(l_ref.item(), rel=1e-5)
     ref_g = hf.transformer.h[0].mlp.c_fc.weight.grad.t()
     assert torch.allclose(ours.blocks[0].mlp_fc.weight.grad, ref_g, rtol=1e-3, atol=1e-6)
+
+
+def test_trained_weights_export_to_transformers():
+    """Train a few steps with the native engine, export with full_state_dict + to_hf_state_dict, load into a fresh
+    transformers model: its logits must equal our module model's logits on the same weights."""
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.models import build_torch_model
+    from distributed_llm_training_gpu_manager_b200.models.hf import config_from_hf, to_hf_state_dict
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+    hc, hf = _tiny_hf()
+    cfg = config_from_hf(hc)
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+        wall_clock_breakdown=False))
+    eng = NativeLlamaEngine(cfg, ds, seq_len=32, device=torch.device("cpu"), seed=2)
+    g = torch.Generator().manual_seed(0)
+    for _ in range(3):
+        ids = torch.randint(0, 1000, (2, 32), generator=g)
+        eng.train_step(ids, ids)
+    named = eng.full_state_dict()
+    hf.load_state_dict(to_hf_state_dict(named, cfg), strict=True)
+    ours = build_torch_model(cfg).float().eval()
+    ours.load_state_dict(named, strict=True)
+    ids = torch.randint(0, 1000, (2, 32), generator=g)
+    with torch.no_grad():
+        assert (hf(input_ids=ids).logits - ours(ids)[..., :1000]).abs().max().item() < 1e-4
