@@ -496,6 +496,16 @@ class ZeroEngine:
         with self.timers.phase("forward"):
             return self.module(*args, **kwargs)
 
+    @torch.no_grad()
+    def eval_loss(self, *args, **kwargs) -> torch.Tensor:
+        """Validation loss of one batch: the module's forward under ``no_grad`` (no gradient hooks fire)."""
+        was_training = self.module.training
+        self.module.eval()
+        try:
+            return self.forward(*args, **kwargs)
+        finally:
+            self.module.train(was_training)
+
     def backward(self, loss: torch.Tensor) -> None:
         cfg = self.cfg
         self._in_backward = True

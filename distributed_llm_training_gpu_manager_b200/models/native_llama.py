@@ -364,6 +364,38 @@ class NativeLlamaEngine(ZeroEngine):
                               dw_out=self._gw(l, "attn_norm"), dw_accumulate=acc, dx_out=dh1)
         return dx
 
+    @torch.no_grad()
+    def eval_loss(self, ids: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """Mean token loss of one batch without touching gradients or saved activations (validation loss for the
+        loss monitor). Same kernels as ``forward``; the LM head runs chunk by chunk without its dgrad / wgrad."""
+        c = self.mcfg
+        B, S = ids.shape
+        assert S == self.seq_len, f"engine built for seq_len={self.seq_len}, got {S}"
+        self._B = B
+        T = B * S
+        if self.pooled_params:
+            self._ensure_resident(0)
+        elif self._adam_stream is not None:
+            evt = self._prefetch_evt.pop(0, None)
+            if evt is not None:
+                torch.cuda.current_stream().wait_event(evt)
+        ids_flat, labels_flat = ids.reshape(-1), labels.reshape(-1)
+        x = E.embedding_fwd(ids_flat, self.param_view("embed.weight"))
+        for l in range(c.n_layers):
+            if self.pooled_params and not self._ag_fused and l + 2 <= c.n_layers:
+                self._prefetch(l + 2)
+            x, _ = self._block_fwd(l, x, keep=False)
+        hf, _, _ = E.rmsnorm_fwd(x, self.param_view("final_norm.weight"), c.norm_eps)
+        w_head = self.param_view("lm_head.weight")
+        loss_tok = torch.empty(T, dtype=torch.float32, device=hf.device)
+        for t0 in range(0, T, self.head_chunk):
+            t1 = min(T, t0 + self.head_chunk)
+            logits = G.linear_fwd(hf[t0:t1], w_head)
+            loss_tok[t0:t1] = E.cross_entropy_(logits, labels_flat[t0:t1], write_grad=False)
+            del logits
+        n_valid = (labels_flat >= 0).sum().clamp(min=1).float()
+        return loss_tok.sum() / n_valid
+
     # -------------------------------------------------------------- protocol
     def forward(self, ids: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         c, cfg = self.mcfg, self.cfg

@@ -146,3 +146,27 @@ def test_adam_overlap_is_bit_identical():
     root = str(Path(__file__).resolve().parent.parent)
     res = subprocess.run([sys.executable, "-c", _OVERLAP_CHECK % root], capture_output=True, text=True, timeout=600)
     assert "ADAM_OVERLAP_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
+
+
+def test_eval_loss_matches_forward_and_leaves_state_alone():
+    from distributed_llm_training_gpu_manager_b200.engine import initialize
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+        wall_clock_breakdown=False))
+    mc = get_config("llama-tiny")
+    eng = NativeLlamaEngine(mc, ds, seq_len=64, device=torch.device("cpu"), seed=4)
+    g = torch.Generator().manual_seed(0)
+    ids = torch.randint(0, mc.vocab_size, (2, 64), generator=g)
+    eng.train_step(ids, ids)
+    before = eng.grad_view("lm_head.weight").clone()
+    ev = float(eng.eval_loss(ids, ids))
+    assert torch.equal(before, eng.grad_view("lm_head.weight"))          # evaluation does not touch gradients
+    assert eng._saved is None
+    assert ev == pytest.approx(float(eng.forward(ids, ids)), rel=1e-6)
+    # the generic nn.Module engine offers the same call
+    torch.manual_seed(0)
+    mod = initialize(build_torch_model(get_config("gpt2-tiny")), ds, device=torch.device("cpu"))
+    x = torch.randint(0, 512, (2, 32), generator=g)
+    a = float(mod.eval_loss(x, x))
+    assert a == pytest.approx(float(mod(x, x)), rel=1e-5) and mod.module.training
