@@ -43,6 +43,9 @@ class TrainerConfig:
     policy: HaltPolicy = field(default_factory=HaltPolicy)
     metrics_path: Optional[str] = None       # JSONL of per-step metrics (rank 0)
     report_url: Optional[str] = None         # POST metrics to /api/v1/monitoring/ingest/single
+    eval_batches: Optional[Callable[[int], Tuple]] = None    # eval_batches(k) -> (args tuple) of the k-th validation batch
+    eval_every: int = 0                      # validation every N optimizer steps (0 = never)
+    eval_steps: int = 1                      # validation batches per evaluation
 
 
 @dataclass
@@ -132,6 +135,18 @@ class Trainer:
         self._log(f"rolled back to {tag} (fault at step {bad_step}); resuming at step {self.engine.global_steps}")
         return True
 
+    def _validate(self) -> float:
+        """Mean validation loss over ``eval_steps`` batches, averaged over the data-parallel ranks."""
+        eng, c = self.engine, self.cfg
+        tot = torch.zeros(1, dtype=torch.float32, device=eng.device)
+        for k in range(max(c.eval_steps, 1)):
+            tot += eng.eval_loss(*c.eval_batches(k)).detach().float().reshape(1)
+        tot /= max(c.eval_steps, 1)
+        if dist.is_available() and dist.is_initialized() and eng.world_size > 1:
+            dist.all_reduce(tot)
+            tot /= eng.world_size
+        return float(tot)
+
     # ------------------------------------------------------------------
     def run(self) -> TrainResult:
         eng, c = self.engine, self.cfg
@@ -160,6 +175,8 @@ class Trainer:
             steps_run += 1
             rec = dict(metrics, step_ms=(time.perf_counter() - t_step0) * 1e3, action=action.value,
                        alerts=[a.alert_type for a in alerts])
+            if c.eval_batches is not None and c.eval_every and metrics["step"] % c.eval_every == 0:
+                rec["val_loss"] = self._validate()
             rec.pop("timers_ms", None)
             self._history.append(rec)
             if mf:

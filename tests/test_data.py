@@ -97,3 +97,24 @@ def test_trainer_on_token_file(tmp_path):
     assert res.status == "finished"
     losses = [h["loss"] for h in res.history]
     assert losses[-1] < losses[0] * 0.8
+
+
+def test_trainer_validation_loss(tmp_path):
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.engine import initialize
+    from distributed_llm_training_gpu_manager_b200.engine.trainer import Trainer, TrainerConfig, synthetic_batches
+    from distributed_llm_training_gpu_manager_b200.models import build_torch_model, get_config
+    mc = get_config("gpt2-tiny")
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=1, offload_optimizer="none", offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=4, gradient_accumulation_steps=1, learning_rate=3e-3, warmup_steps=2,
+        wall_clock_breakdown=False))
+    torch.manual_seed(0)
+    eng = initialize(build_torch_model(mc), ds, device=torch.device("cpu"))
+    train = synthetic_batches(mc.vocab_size, 4, 32, "cpu", seed=1)
+    val = synthetic_batches(mc.vocab_size, 4, 32, "cpu", seed=99)
+    res = Trainer(eng, train, TrainerConfig(total_steps=12, log_every=1000, eval_batches=val, eval_every=4,
+                                            eval_steps=2)).run()
+    vals = [(h["step"], h["val_loss"]) for h in res.history if "val_loss" in h]
+    assert [s for s, _ in vals] == [4, 8, 12]
+    assert vals[-1][1] < vals[0][1]                                              # the learnable stream generalises
