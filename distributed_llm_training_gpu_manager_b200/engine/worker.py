@@ -46,6 +46,9 @@ def main(argv=None) -> int:
     ap.add_argument("--seed", type=int, default=1234)
     ap.add_argument("--data", default=None, help="flat binary token file (uint16/uint32); default: synthetic tokens")
     ap.add_argument("--data_dtype", default="auto", help="auto | uint16 | uint32 | int32 | int64")
+    ap.add_argument("--eval_data", default=None, help="token file for the validation loss")
+    ap.add_argument("--eval_every", type=int, default=0)
+    ap.add_argument("--eval_steps", type=int, default=4)
     ns = ap.parse_args(argv)
     if os.environ.get("B200ZERO_HANG_DUMP"):  # debugging aid: dump all stacks and exit after N seconds
         import faulthandler
@@ -75,8 +78,14 @@ def main(argv=None) -> int:
                                 dtype=ns.data_dtype, vocab_size=mcfg.vocab_size)
     else:
         batches = synthetic_batches(mcfg.vocab_size, ecfg.micro_batch, seq, device, rank, world, seed=ns.seed)
+    eval_batches = None
+    if ns.eval_data and ns.eval_every:
+        from .data import token_batches
+        eval_batches = token_batches(ns.eval_data, ecfg.micro_batch, seq, device, rank, world, seed=ns.seed + 1,
+                                     shuffle=False, dtype=ns.data_dtype, vocab_size=mcfg.vocab_size, prefetch=0)
     tcfg = TrainerConfig(total_steps=ns.steps, save_dir=ns.save_dir, save_every=ns.save_every,
-                         metrics_path=ns.metrics, monitor=MonitorConfig(window_size=ns.window), log_every=10)
+                         metrics_path=ns.metrics, monitor=MonitorConfig(window_size=ns.window), log_every=10,
+                         eval_batches=eval_batches, eval_every=ns.eval_every, eval_steps=ns.eval_steps)
     res = Trainer(engine, batches, tcfg).run()
     if rank == 0 and ns.result:
         with open(ns.result, "w") as f:
