@@ -46,6 +46,8 @@ def main(argv=None) -> int:
     ap.add_argument("--seed", type=int, default=1234)
     ap.add_argument("--data", default=None, help="flat binary token file (uint16/uint32); default: synthetic tokens")
     ap.add_argument("--data_dtype", default="auto", help="auto | uint16 | uint32 | int32 | int64")
+    ap.add_argument("--init_hf", default=None,
+                    help="directory of a Hugging Face Llama / GPT-2 checkpoint to start from (architecture taken from its config)")
     ap.add_argument("--eval_data", default=None, help="token file for the validation loss")
     ap.add_argument("--eval_every", type=int, default=0)
     ap.add_argument("--eval_steps", type=int, default=4)
@@ -60,7 +62,21 @@ def main(argv=None) -> int:
     from .config import load_config
     from .trainer import Trainer, TrainerConfig, synthetic_batches
 
-    mcfg = get_config(ns.model)
+    hf_named = None
+    if ns.init_hf:
+        # every rank reads the checkpoint and keeps its own rows (load_full_params); fine for one node with host RAM to spare
+        from transformers import AutoModelForCausalLM
+        from ..models import hf as hfmod
+        hf_model = AutoModelForCausalLM.from_pretrained(ns.init_hf, torch_dtype=torch.float32)
+        if hf_model.config.model_type == "gpt2":
+            mcfg = hfmod.gpt2_config_from_hf(hf_model.config)
+            hf_named = hfmod.gpt2_from_hf_state_dict(hf_model.state_dict(), mcfg)
+        else:
+            mcfg = hfmod.config_from_hf(hf_model.config)
+            hf_named = hfmod.from_hf_state_dict(hf_model.state_dict(), mcfg)
+        del hf_model
+    else:
+        mcfg = get_config(ns.model)
     ecfg = load_config(ns.deepspeed_config)
     seq = ns.seq_len or min(mcfg.max_seq, 128)
     torch.manual_seed(ns.seed)
@@ -72,6 +88,12 @@ def main(argv=None) -> int:
     else:
         from .zero import ZeroEngine
         engine = ZeroEngine(build_torch_model(mcfg), ecfg, device=device, comm=ns.comm)
+    if hf_named is not None:
+        if engine.source is not None:
+            engine.load_full_params(hf_named)
+        else:       # nn.Module engine: parameters are views of the engine's buffers, loaded through the same call
+            engine.load_full_params({k: v for k, v in hf_named.items() if k in engine.layout.by_name}, strict=False)
+        del hf_named
     if ns.data:
         from .data import token_batches
         batches = token_batches(ns.data, ecfg.micro_batch, seq, device, rank, world, seed=ns.seed,

@@ -162,3 +162,29 @@ def test_trained_weights_export_to_transformers():
     ids = torch.randint(0, 1000, (2, 32), generator=g)
     with torch.no_grad():
         assert (hf(input_ids=ids).logits - ours(ids)[..., :1000]).abs().max().item() < 1e-4
+
+
+def test_worker_starts_from_a_hugging_face_checkpoint(tmp_path):
+    """`--init_hf DIR`: architecture and weights come from a transformers checkpoint directory; the first reported
+    loss equals the loss transformers computes on the worker's first (synthetic) batch with those weights."""
+    import json
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.engine import worker
+    from distributed_llm_training_gpu_manager_b200.engine.trainer import synthetic_batches
+    hc, hf = _tiny_hf()
+    hf.save_pretrained(tmp_path / "ckpt", safe_serialization=True)
+    launcher = DeepSpeedLauncher()
+    cfg_path = launcher.write_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-4, warmup_steps=1,
+        wall_clock_breakdown=False), str(tmp_path / "ds.json"))
+    out = tmp_path / "result.json"
+    assert worker.main(["--deepspeed_config", cfg_path, "--init_hf", str(tmp_path / "ckpt"), "--engine", "native",
+                        "--steps", "2", "--seq_len", "32", "--result", str(out)]) == 0
+    res = json.loads(out.read_text())
+    ids, labels = synthetic_batches(1000, 2, 32, "cpu", 0, 1, seed=1234)(0)
+    with torch.no_grad():
+        z = hf(input_ids=ids).logits.view(-1, 1000)
+        lse = torch.logsumexp(torch.cat([z, torch.zeros(z.shape[0], 24)], 1), 1)      # 24 zero rows of vocabulary padding
+        ref = (lse - z.gather(1, labels.view(-1, 1)).squeeze(1)).mean().item()
+    assert res["losses"][0] == pytest.approx(ref, rel=1e-4)
