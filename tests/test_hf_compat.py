@@ -188,3 +188,33 @@ def test_worker_starts_from_a_hugging_face_checkpoint(tmp_path):
         lse = torch.logsumexp(torch.cat([z, torch.zeros(z.shape[0], 24)], 1), 1)      # 24 zero rows of vocabulary padding
         ref = (lse - z.gather(1, labels.view(-1, 1)).squeeze(1)).mean().item()
     assert res["losses"][0] == pytest.approx(ref, rel=1e-4)
+
+
+def test_checkpoint_consolidates_into_transformers_layout(tmp_path):
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.engine import checkpoint as ckpt, zero_to_fp32
+    from distributed_llm_training_gpu_manager_b200.models.hf import config_from_hf
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+    hc, hf = _tiny_hf()
+    hc.save_pretrained(tmp_path / "cfg")
+    cfg = config_from_hf(hc)
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+        wall_clock_breakdown=False))
+    eng = NativeLlamaEngine(cfg, ds, seq_len=32, device=torch.device("cpu"), seed=2)
+    ids = torch.randint(0, 1000, (2, 32))
+    eng.train_step(ids, ids)
+    eng.save_checkpoint(str(tmp_path / "ck"), tag="s1")
+    ckpt.wait_for_pending_writes()
+    assert zero_to_fp32.main([str(tmp_path / "ck"), str(tmp_path / "hf.pt"), "--hf_config", str(tmp_path / "cfg" / "config.json")]) == 0
+    hf.load_state_dict(torch.load(tmp_path / "hf.pt"), strict=True)
+    with torch.no_grad():
+        z = hf(input_ids=ids).logits.view(-1, 1000)
+    # same weights -> the engine's validation loss equals transformers' loss up to the 24 padded vocabulary rows
+    with torch.no_grad():
+        pad_logits = torch.nn.functional.linear(hf.model(input_ids=ids).last_hidden_state.view(-1, 256),
+                                                eng.full_param("lm_head.weight")[1000:])
+    lse_full = torch.logsumexp(torch.cat([z, pad_logits], 1), 1)
+    ref = (lse_full - z.gather(1, ids.view(-1, 1)).squeeze(1)).mean().item()
+    assert float(eng.eval_loss(ids, ids)) == pytest.approx(ref, rel=1e-4)
