@@ -485,6 +485,10 @@ def run_ours(args) -> int:
         "final_loss": last["loss"] if last else None,
         "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 1),
     }
+    opt_ins = {k: v for k, v in sorted(os.environ.items())
+               if k.startswith("B200ZERO_") and not k.startswith(("B200ZERO_BENCH_", "B200ZERO_HEARTBEAT", "B200ZERO_JOB"))}
+    if opt_ins:
+        out["config"]["env_switches"] = opt_ins          # which non-default kernels / schedules this run used
     if args.fallback_note:
         out["fallback"] = args.fallback_note
     if breakdown is not None:
