@@ -336,6 +336,10 @@ def run_ours(args) -> int:
     device = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if args.comm != "nccl" and args.impl != "nccl":
+            # our arm uses NCCL for bootstrap and 16-byte control messages only: skip its NVLS (multicast) set-up,
+            # which costs seconds at 8 ranks and depends on fabric state left behind by earlier jobs
+            os.environ.setdefault("NCCL_NVLS_ENABLE", "0")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
     beat("pg")
 
@@ -485,6 +489,8 @@ def run_ours(args) -> int:
         "final_loss": last["loss"] if last else None,
         "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 1),
     }
+    if world > 1:
+        out["config"]["nccl_nvls"] = os.environ.get("NCCL_NVLS_ENABLE", "default")
     opt_ins = {k: v for k, v in sorted(os.environ.items())
                if k.startswith("B200ZERO_") and not k.startswith(("B200ZERO_BENCH_", "B200ZERO_HEARTBEAT", "B200ZERO_JOB"))}
     if opt_ins:
