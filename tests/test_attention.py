@@ -137,7 +137,7 @@ def test_flash_fwd_v3_matches_reference():
     import sys
     from pathlib import Path
     root = str(Path(__file__).resolve().parent.parent)
-    res = subprocess.run([sys.executable, "-c", _V3_CHECK % root], capture_output=True, text=True, timeout=300,
+    res = subprocess.run([sys.executable, "-c", _V3_CHECK % root], capture_output=True, text=True, timeout=150,
                          env=dict(os.environ))
     out_dir = Path(root) / "gpurun_out"
     try:
@@ -201,7 +201,7 @@ def test_flash_bwd_v3_matches_reference():
     import sys
     from pathlib import Path
     root = str(Path(__file__).resolve().parent.parent)
-    res = subprocess.run([sys.executable, "-c", _BWD_V3_CHECK % root], capture_output=True, text=True, timeout=300,
+    res = subprocess.run([sys.executable, "-c", _BWD_V3_CHECK % root], capture_output=True, text=True, timeout=150,
                          env=dict(os.environ))
     try:
         (Path(root) / "gpurun_out").mkdir(exist_ok=True)

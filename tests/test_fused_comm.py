@@ -318,6 +318,6 @@ def test_pull_allgather_v2_matches_v1_emulated():
     import sys
     from pathlib import Path
     root = str(Path(__file__).resolve().parent.parent)
-    res = subprocess.run([sys.executable, "-c", _PULL_V2_CHECK % root], capture_output=True, text=True, timeout=300,
+    res = subprocess.run([sys.executable, "-c", _PULL_V2_CHECK % root], capture_output=True, text=True, timeout=150,
                          env=dict(os.environ))
     assert "PULL_V2_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]

@@ -144,7 +144,7 @@ def test_adam_overlap_is_bit_identical():
     import sys
     from pathlib import Path
     root = str(Path(__file__).resolve().parent.parent)
-    res = subprocess.run([sys.executable, "-c", _OVERLAP_CHECK % root], capture_output=True, text=True, timeout=600)
+    res = subprocess.run([sys.executable, "-c", _OVERLAP_CHECK % root], capture_output=True, text=True, timeout=150)
     assert "ADAM_OVERLAP_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
 
 

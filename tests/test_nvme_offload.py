@@ -200,5 +200,5 @@ def test_nvme_engine_matches_device_engine_gpu(tmp_path):
     from pathlib import Path
     root = str(Path(__file__).resolve().parent.parent)
     res = subprocess.run([sys.executable, "-c", _GPU_CHECK % (root, str(tmp_path))], capture_output=True, text=True,
-                         timeout=600)
+                         timeout=150)
     assert "NVME_GPU_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
