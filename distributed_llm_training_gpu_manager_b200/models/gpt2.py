@@ -28,17 +28,18 @@ class GPT2Block(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         B, S, D = x.shape
-        own = G2.enabled_for(x)       # LayerNorm / bias+GELU through csrc/gpt2_ops.cu instead of torch eager
+        own = G2.enabled_for(x)       # LayerNorm / bias+GELU (csrc/gpt2_ops.cu) and the tcgen05 GEMM instead of torch ops
+        lin = (lambda m, t: G2.linear(t, m.weight, m.bias)) if own else (lambda m, t: m(t))
         h = G2.layer_norm(x, self.ln_1.weight, self.ln_1.bias, self.ln_1.eps) if own else self.ln_1(x)
-        q, k, v = self.attn_qkv(h).view(B, S, 3, self.n_heads, D // self.n_heads).unbind(2)
+        q, k, v = lin(self.attn_qkv, h).view(B, S, 3, self.n_heads, D // self.n_heads).unbind(2)
         a = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), is_causal=True)
-        x = x + self.attn_proj(a.transpose(1, 2).reshape(B, S, D))
+        x = x + lin(self.attn_proj, a.transpose(1, 2).reshape(B, S, D))
         if own:
             h = G2.layer_norm(x, self.ln_2.weight, self.ln_2.bias, self.ln_2.eps)
-            u = G2.bias_gelu(F.linear(h, self.mlp_fc.weight), self.mlp_fc.bias)
+            u = G2.bias_gelu(G2.linear(h, self.mlp_fc.weight), self.mlp_fc.bias)
         else:
             u = F.gelu(self.mlp_fc(self.ln_2(x)), approximate="tanh")
-        return x + self.mlp_proj(u)
+        return x + lin(self.mlp_proj, u)
 
 
 class GPT2(nn.Module):

@@ -167,6 +167,41 @@ class BiasGeluFn(torch.autograd.Function):
         return dx.view(dy.shape), db.to(b.dtype)
 
 
+class LinearFn(torch.autograd.Function):
+    """``y = x·Wᵀ (+ b)`` on the tcgen05 GEMM (``ops/gemm.py``: forward NT, dgrad NN, wgrad TN — no transposes);
+    the bias add and its gradient (a column sum) stay element-wise torch ops."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        from . import gemm as G
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        ctx.save_for_backward(x2, w)
+        ctx.has_bias = b is not None
+        y = G.linear_fwd(x2, w)
+        if b is not None:
+            y = y + b
+        return y.view(*shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import gemm as G
+        x2, w = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = G.linear_dgrad(dy2, w)
+        dw = G.linear_wgrad(dy2, x2, out_dtype=w.dtype)
+        db = dy2.sum(0).to(w.dtype) if ctx.has_bias else None
+        return dx.view(*dy.shape[:-1], w.shape[1]), dw, db
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
+    return LinearFn.apply(x, w, b)
+
+
 def layer_norm(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
     return LayerNormFn.apply(x, w, b, eps)
 

@@ -101,3 +101,18 @@ def test_gpt2_kernels_match_reference_on_gpu():
     res = subprocess.run([sys.executable, "-c", _GPU_CHECK % str(ROOT)], capture_output=True, text=True, timeout=150,
                          env=dict(os.environ))
     assert "GPT2_OPS_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
+
+
+def test_linear_function_matches_torch_autograd():
+    torch.manual_seed(4)
+    x = torch.randn(3, 5, 24).requires_grad_()
+    w = torch.randn(40, 24).requires_grad_()
+    b = torch.randn(40).requires_grad_()
+    dy = torch.randn(3, 5, 40)
+    g = torch.autograd.grad(G2.linear(x, w, b), (x, w, b), dy)
+    h = torch.autograd.grad(F.linear(x, w, b), (x, w, b), dy)
+    for u, v in zip(g, h):
+        assert torch.allclose(u, v, atol=1e-4, rtol=1e-4)
+    g2 = torch.autograd.grad(G2.linear(x, w), (x, w), dy)
+    h2 = torch.autograd.grad(F.linear(x, w), (x, w), dy)
+    assert all(torch.allclose(u, v, atol=1e-4, rtol=1e-4) for u, v in zip(g2, h2))
