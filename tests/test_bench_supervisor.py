@@ -13,7 +13,7 @@ ROOT = Path(__file__).resolve().parent.parent
 
 
 def _run(mode, port):
-    env = dict(os.environ, B200ZERO_BENCH_FAKE=mode, B200ZERO_BENCH_QUIET_S="5", B200ZERO_BENCH_STARTUP_S="60",
+    env = dict(os.environ, B200ZERO_BENCH_FAKE=mode, B200ZERO_BENCH_QUIET_S="3", B200ZERO_BENCH_STARTUP_S="60",
                OMP_NUM_THREADS="1")
     res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
                           "--master-addr", "127.0.0.1", "--master-port", str(port), str(ROOT / "bench.py"),
