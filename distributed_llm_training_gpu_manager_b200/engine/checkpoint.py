@@ -150,6 +150,10 @@ def _stage_to_host(engine, tensors: Dict[str, torch.Tensor]) -> Tuple[Dict[str, 
 def save_checkpoint(engine, save_dir: str, tag: Optional[str] = None, client_state: Optional[Dict] = None,
                     async_write: bool = False, keep_last: Optional[int] = None) -> str:
     cfg = engine.cfg
+    # The pinned staging buffers are shared by every save of this engine: a write still in flight (rank 0's writer
+    # can sit for minutes waiting for the other ranks' markers) must finish before they are overwritten, otherwise
+    # the earlier checkpoint is torn and its checksum — computed after the write — would still verify.
+    _writer.wait()
     tag = tag or f"global_step{engine.global_steps}"
     root = Path(save_dir)
     tdir = root / tag
@@ -183,6 +187,9 @@ def save_checkpoint(engine, save_dir: str, tag: Optional[str] = None, client_sta
     param_shapes = [{s["name"]: tuple(s["shape"]) for u in layout_desc["units"] for s in u["params"]}]
     monitor_sd = (client_state or {}).get("monitor")
     step_no = engine.global_steps - engine.skipped_steps
+    global_steps = engine.global_steps
+    scaler_sd, scaler_dynamic = dict(engine.scaler.state_dict()), engine.scaler.dynamic   # call-time snapshot
+    client_state = dict(client_state or {})
 
     def write() -> None:
         if evt is not None:
@@ -190,8 +197,8 @@ def save_checkpoint(engine, save_dir: str, tag: Optional[str] = None, client_sta
         files: List[Path] = []
         optim_sd = {
             "optimizer_state_dict": {
-                "zero_stage": engine.stage, "partition_count": ws, "loss_scaler": engine.scaler.state_dict(),
-                "dynamic_loss_scale": engine.scaler.dynamic, "overflow": False,
+                "zero_stage": engine.stage, "partition_count": ws, "loss_scaler": scaler_sd,
+                "dynamic_loss_scale": scaler_dynamic, "overflow": False,
                 "base_optimizer_state": {
                     "state": {0: {"step": step_no, "exp_avg": staged["exp_avg"], "exp_avg_sq": staged["exp_avg_sq"]}},
                     "param_groups": [{"lr": cfg.lr, "betas": tuple(cfg.betas), "eps": cfg.eps,
@@ -224,7 +231,7 @@ def save_checkpoint(engine, save_dir: str, tag: Optional[str] = None, client_sta
                 time.sleep(0.02)
             else:
                 raise TimeoutError(f"ranks did not finish writing {tdir}")
-            manifest = {"tag": tag, "global_steps": engine.global_steps, "world_size": ws, "zero_stage": engine.stage,
+            manifest = {"tag": tag, "global_steps": global_steps, "world_size": ws, "zero_stage": engine.stage,
                         "precision": cfg.precision, "created": time.time(), "files": {}}
             for r in range(ws):
                 manifest["files"].update(json.loads((tdir / f".done_rank{r}").read_text()))
@@ -383,6 +390,12 @@ def load_checkpoint(engine, load_dir: str, tag: Optional[str] = None, verify: bo
     for gb in {b.data_ptr(): b for b in engine._unit_gbuf}.values():
         gb.zero_()
     engine._loss_accum.zero_()
+    if _dist_ready() and engine.world_size > 1:
+        # the fused gathers read the peers' shard_params directly over NVLink: every rank's restored rows must be
+        # in memory before anyone gathers (same rule as ZeroEngine.load_full_params)
+        if engine.on_cuda:
+            torch.cuda.synchronize(engine.device)
+        dist.barrier()
     if engine.stage >= 3 and engine.pooled_params:
         engine._resident = [False] * len(engine.layout.units)
         engine._slot_owner = [None, None]

@@ -80,7 +80,11 @@ class Trainer:
             pass
 
     def _on_sigterm(self, signum, frame) -> None:
+        # Only a request: ranks can see the signal on different sides of a step boundary, and the emergency save is
+        # collective. The engine carries the bit through the step's stats all-reduce; every rank then acts on the
+        # agreed value in the same iteration (``metrics["preempt"]``).
         self._preempted = True
+        self.engine.preempt_requested = True
 
     # ------------------------------------------------------------------
     def _maybe_resume(self) -> bool:
@@ -197,7 +201,7 @@ class Trainer:
                     continue
                 status = "halted"
                 break
-            if self._preempted:
+            if metrics.get("preempt", self._preempted):
                 self._save(tag=f"preempt_step{eng.global_steps}", sync=True)
                 status = "preempted"
                 break

@@ -173,6 +173,9 @@ class ZeroEngine:
                 comm = self.comm_mode = "fused"
         self._in_backward = False
         self._reduce_now = True
+        # Set by whoever learns that this rank is about to lose its machine (SIGTERM handler, spot probe). The bit rides
+        # in the per-step stats all-reduce, so every rank sees the same answer at the same step boundary.
+        self.preempt_requested = False
         self._prefetch_evt: Dict[int, Any] = {}
         self._adam_stream = None            # set by _enable_adam_overlap()
 
@@ -340,7 +343,7 @@ class ZeroEngine:
         self._norm = torch.zeros(1, dtype=torch.float32, device=dev)
         self._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
         if self.on_cuda:
-            self._stats_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+            self._stats_host = torch.zeros(5, dtype=torch.float32).pin_memory()
         if self.stage >= 3 and self.pooled_params:
             self._gather_unit(0)
 
@@ -557,12 +560,16 @@ class ZeroEngine:
                     O.sumsq(self.shard_grads[L.part_numel:], st[3:4], nonfinite_flag=self._flag)
             st[1] = self._flag.float()[0]
             st[2] = self._loss_accum[0] / self.world_size
+            want_stop = 1.0 if self.preempt_requested else 0.0
             if self.world_size > 1:
                 repl = st[3].clone()
-                st[3] = 0
+                st[3] = want_stop             # fourth slot: "some rank was told to stop" (summed, so > 0 means yes)
                 if self.fused is None or not self.fused.allreduce_stats(st):
                     dist.all_reduce(st)       # Σ‖g‖² (X6), overflow flag (X5), mean loss (X8) in one message
+                stop_votes = st[3].clone()
                 st[3] = repl
+            else:
+                stop_votes = torch.full((), want_stop, dtype=torch.float32, device=self.device)
             self._sumsq[0] = st[0] + st[3]
             self._flag[0] = (st[1] > 0).int()
             inv_scale = 1.0 / self.scaler.scale
@@ -590,12 +597,13 @@ class ZeroEngine:
                 self.shard_grads.zero_()       # (the fused Adam kernel zeroes the shard as it reads it)
             # host read: the one sync of the step (feeds the loss monitor)
             if self.on_cuda:
-                self._stats_host.copy_(torch.stack([self._sumsq[0], self._flag[0].float(), st[2], self._norm[0] * inv_scale]),
-                                       non_blocking=True)
+                self._stats_host.copy_(torch.stack([self._sumsq[0], self._flag[0].float(), st[2], self._norm[0] * inv_scale,
+                                                    stop_votes]), non_blocking=True)
                 torch.cuda.current_stream().synchronize()
                 vals = self._stats_host.tolist()
             else:
-                vals = [float(self._sumsq[0]), float(self._flag[0]), float(st[2]), float(self._norm[0]) * inv_scale]
+                vals = [float(self._sumsq[0]), float(self._flag[0]), float(st[2]), float(self._norm[0]) * inv_scale,
+                        float(stop_votes)]
             self._flag.zero_()                 # clean for the next step's reduce / norm kernels
             overflow = vals[1] > 0
             self.scaler.update(overflow)
@@ -616,7 +624,8 @@ class ZeroEngine:
         self.global_steps += 1
         self.schedule.last_step = self.global_steps
         m = {"step": self.global_steps, "loss": vals[2], "grad_norm": vals[3], "grad_norm_sq": vals[3] ** 2,
-             "nonfinite": overflow, "lr": lr, "loss_scale": self.scaler.scale, "skipped": overflow}
+             "nonfinite": overflow, "lr": lr, "loss_scale": self.scaler.scale, "skipped": overflow,
+             "preempt": vals[4] > 0}
         if cfg.wall_clock_breakdown:
             m["timers_ms"] = self.timers.collect()
         self.last_metrics = m

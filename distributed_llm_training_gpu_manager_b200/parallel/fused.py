@@ -18,16 +18,28 @@ from typing import Dict, List, Optional
 
 import torch
 
+from ..engine.partition import _up
 from ..ops import lib as _lib
 from .symm import SymmetricBuffer, nvls_buffer_or_none
 
 RS_CHANNEL, ADAM_CHANNEL, STATS_CHANNEL = 0, 1, 2
 
 
+def seg_len(spec, world_size: int) -> int:
+    """Element count a fused kernel walks for one tensor. The kernels move 8-element (16-byte) vectors, so a
+    replicated tensor is handed over with its zero-filled padding (the layout pads every tensor to ``ALIGN``
+    elements in the unit buffers and in the shard alike); a partitioned one must split into whole vectors."""
+    if spec.partitioned:
+        assert (spec.numel // world_size) % 8 == 0, f"{spec.name}: per-rank slice is not a whole number of vectors"
+        return spec.numel
+    return _up(spec.numel)
+
+
 def segment_table(records: List[tuple], device) -> torch.Tensor:
     """records: (full_off, numel, shard_off, partitioned) -> int64 [n, 4] device tensor whose rows
     are the 32-byte Segment structs of csrc/fused_comm.cu."""
     rows = [[fo, n, so, int(bool(part))] for fo, n, so, part in records]   # int32 partitioned + int32 pad = 1 int64 (LE)
+    assert all(r[1] % 8 == 0 for r in rows), "fused kernels walk whole 8-element vectors"
     return torch.tensor(rows, dtype=torch.int64, device=device).contiguous()
 
 
@@ -60,7 +72,7 @@ class FusedComm:
         self._unit_segs: Dict[int, torch.Tensor] = {}
         for u in L.units:
             self._unit_segs[u.index] = segment_table(
-                [(s.full_offset, s.numel, s.shard_offset, s.partitioned) for s in u.params], dev)
+                [(s.full_offset, seg_len(s, engine.world_size), s.shard_offset, s.partitioned) for s in u.params], dev)
         self.launches = 0
         self.nvls_launches = 0
 
@@ -156,14 +168,16 @@ class FusedComm:
             if not hasattr(self, "_all_segs"):
                 recs, off = [], 0
                 for u in e.layout.units:
-                    recs += [(off + s.full_offset, s.numel, s.shard_offset, s.partitioned) for s in u.params]
+                    recs += [(off + s.full_offset, seg_len(s, e.world_size), s.shard_offset, s.partitioned)
+                             for s in u.params]
                     off += u.full_numel
                 self._all_segs = segment_table(recs, e.device)
                 self._all_ptrs = self._ptrs_for(e._pbuf_all)
             segs, nseg, pptrs = self._all_segs, self._all_segs.shape[0], self._all_ptrs
         else:
             if not hasattr(self, "_all_segs"):
-                recs = [(0, s.numel, s.shard_offset, s.partitioned) for u in e.layout.units for s in u.params]
+                recs = [(0, seg_len(s, e.world_size), s.shard_offset, s.partitioned)
+                        for u in e.layout.units for s in u.params]
                 self._all_segs = segment_table(recs, e.device)
             segs, nseg, pptrs = self._all_segs, self._all_segs.shape[0], None
         tail = (segs.data_ptr(), nseg, e.master.data_ptr(), e.exp_avg.data_ptr(),

@@ -1,0 +1,106 @@
+"""Regression tests for the round-1 review findings that need no GPU: collective preemption, back-to-back
+asynchronous saves, vector-granular segment tables."""
+import os
+import threading
+import time
+
+import pytest
+import torch
+
+from distributed_llm_training_gpu_manager_b200.engine import checkpoint as ckpt
+from distributed_llm_training_gpu_manager_b200.engine import initialize
+from distributed_llm_training_gpu_manager_b200.engine.partition import build_layout
+from distributed_llm_training_gpu_manager_b200.engine.trainer import Trainer, TrainerConfig, synthetic_batches
+from distributed_llm_training_gpu_manager_b200.parallel.fused import seg_len
+
+from dist_utils import run_ranks
+from test_zero_engine import MB, SEQ, VOCAB, _model, ds_dict
+
+
+# ---------------------------------------------------------------- preemption is agreed between ranks
+def _preempt_rank(rank, world, tmp):
+    eng = initialize(_model(), ds_dict(2), device="cpu")
+    data = synthetic_batches(VOCAB, MB, SEQ, "cpu", rank, world)
+    tr = Trainer(eng, data, TrainerConfig(total_steps=12, save_dir=tmp, save_every=0, async_save=False, log_every=100))
+    orig = eng._optimizer_step
+
+    def step_with_signal():
+        # only rank 1 is told to stop, and only from its 4th step on (a SIGTERM seen on one side of a boundary)
+        if rank == 1 and eng.global_steps == 3:
+            tr._on_sigterm(15, None)
+        return orig()
+    eng._optimizer_step = step_with_signal
+    res = tr.run()
+    return res.status, res.final_step
+
+
+def test_preemption_bit_is_agreed_by_all_ranks(tmp_path):
+    out = run_ranks(_preempt_rank, 2, (str(tmp_path),))
+    assert out[0] == out[1] == ("preempted", 4)          # both ranks stop after the same step
+    assert (tmp_path / "preempt_step4" / "manifest.json").exists()
+    assert ckpt.verify_checkpoint(str(tmp_path), "preempt_step4") == (True, "ok")
+
+
+def test_single_rank_preempt_request_reaches_metrics():
+    eng = initialize(_model(), ds_dict(0), device="cpu")
+    data = synthetic_batches(VOCAB, MB, SEQ, "cpu")
+    eng.backward(eng(*data(0)))
+    assert eng.step()["preempt"] is False
+    eng.preempt_requested = True
+    eng.backward(eng(*data(1)))
+    assert eng.step()["preempt"] is True
+
+
+# ---------------------------------------------------------------- a second save must not tear the first
+def test_async_save_followed_by_second_save_keeps_first_intact(tmp_path, monkeypatch):
+    eng = initialize(_model(), ds_dict(1), device="cpu")
+    data = synthetic_batches(VOCAB, MB, SEQ, "cpu")
+    eng.backward(eng(*data(0))); eng.step()
+    want_master = eng.master.clone()
+    want_scale = dict(eng.scaler.state_dict())
+    slow = threading.Event()
+    real_save = ckpt._atomic_torch_save
+
+    def slow_save(obj, path):
+        if not slow.is_set():
+            slow.set()
+            time.sleep(0.5)                # first writer is still serialising when the second save is requested
+        real_save(obj, path)
+    monkeypatch.setattr(ckpt, "_atomic_torch_save", slow_save)
+    eng.save_checkpoint(str(tmp_path), tag="global_step1", async_write=True)
+    eng.backward(eng(*data(1))); eng.step()
+    eng.save_checkpoint(str(tmp_path), tag="global_step2", async_write=True)
+    ckpt.wait_for_pending_writes()
+    for tag in ("global_step1", "global_step2"):
+        assert ckpt.verify_checkpoint(str(tmp_path), tag) == (True, "ok")
+    sd = torch.load(tmp_path / "global_step1" / ckpt.optim_file(0, False), weights_only=False)["optimizer_state_dict"]
+    assert torch.equal(sd["single_partition_of_fp32_groups"][0], want_master)
+    assert sd["loss_scaler"] == want_scale
+    assert sd["base_optimizer_state"]["state"][0]["step"] == 1
+
+
+# ---------------------------------------------------------------- fused kernels move whole 16-byte vectors
+def test_segment_lengths_are_whole_vectors():
+    specs = [("w", (64, 48), 0), ("bias_odd", (13,), 0), ("vocab_odd", (50257,), 0), ("blk.w", (128, 64), 1)]
+    L = build_layout(specs, ["root", "b0"], world_size=4, partition=True, persistence_threshold=1000)
+    seen = {}
+    for u in L.units:
+        for s in u.params:
+            n = seg_len(s, 4)
+            seen[s.name] = n
+            assert n % 8 == 0
+            if s.partitioned:
+                assert n == s.numel and (n // 4) % 8 == 0
+            else:
+                assert n >= s.numel
+    assert seen["bias_odd"] == 16 and seen["vocab_odd"] == 50272
+    # padded lengths never run into the next tensor of the unit or of the shard
+    for u in L.units:
+        ordered = sorted(u.params, key=lambda s: s.full_offset)
+        for a, b in zip(ordered, ordered[1:]):
+            assert a.full_offset + seg_len(a, 4) <= b.full_offset
+        assert ordered[-1].full_offset + seg_len(ordered[-1], 4) <= u.full_numel
+    repl = sorted((s for u in L.units for s in u.params if not s.partitioned), key=lambda s: s.shard_offset)
+    for a, b in zip(repl, repl[1:]):
+        assert a.shard_offset + seg_len(a, 4) <= b.shard_offset
+    assert repl[-1].shard_offset + seg_len(repl[-1], 4) <= L.shard_numel
