@@ -13,15 +13,22 @@ Weak scaling: per-GPU work (micro-batch × seq) is fixed as N grows. Synthetic t
 weights (no dataset or checkpoint on the box). Weights (16 GB bf16) and optimizer state (96 GB)
 are far larger than the 126 MB L2, so no explicit L2 flush is needed between steps.
 
+Every N does the same work per GPU: the activation policy is pinned (``--recompute``, default ``none`` for
+Llama-3-8B, which fits at every N) instead of being chosen from free memory.
+
 Multi-GPU runs (WORLD_SIZE > 1) execute in one supervised child process per rank (``supervise``): the
 child does all the work and prints the line; the parent watches a heartbeat file. If the default run
 stops making progress (the fused collectives wait on peer flags inside kernels) or dies, it is re-run
-once with ``--comm nccl`` and the line carries a ``"fallback"`` note and ``"comm": "nccl"`` in its
-config. ``B200ZERO_BENCH_SUPERVISE=0`` runs in-process as for N = 1.
+once with ``--comm nccl`` and the line says so three times over: ``"fallback"``, ``"impl": "ours-nccl-fallback"``
+and ``"comm": "nccl"`` in its config. Both attempts together stay inside ``B200ZERO_BENCH_BUDGET_S`` (800 s).
+``B200ZERO_BENCH_SUPERVISE=0`` runs in-process as for N = 1.
 
 ``--impl reference`` runs the unmodified reference from ``baseline/_ref`` through its own public
 API — which can only shell out to a ``deepspeed`` CLI that is not installable offline — and
-reports that outcome.
+reports that outcome. ``--impl torch`` is the library stand-in for that DeepSpeed job: the same
+model, batch, sequence length, clipping and precision on stock PyTorch only — cuBLAS, SDPA, NCCL through FSDP2
+(= ZeRO-3) and ``torch.optim.AdamW(fused=True)`` — timed by the same harness (``baseline/torch_zero3.py``).
+``--impl nccl`` is our engine and kernels with NCCL collectives in place of the fused ones.
 """
 from __future__ import annotations
 
@@ -44,7 +51,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl", "torch"])
     ap.add_argument("--model", default="llama3-8b")
     ap.add_argument("--seq-len", type=int, default=4096)
     ap.add_argument("--micro-batch", type=int, default=2)
@@ -52,6 +59,8 @@ def parse_args():
     ap.add_argument("--zero-stage", type=int, default=3)
     ap.add_argument("--engine", default="auto", help="auto | native | module (generic nn.Module ZeRO engine)")
     ap.add_argument("--attn", default=None, help="attention backend override: native | sdpa")
+    ap.add_argument("--recompute", default=None, help="activation policy: none | light | selective | full | auto "
+                    "(default: none for llama3-8b so that every N does the same work, auto otherwise)")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-halt", action="store_true", help="skip the spike-to-halt measurement after the timed regions")
     ap.add_argument("--breakdown", action="store_true", help="after the timed region, run one extra step with per-phase CUDA-event timers")
@@ -64,19 +73,29 @@ def parse_args():
 
 # --------------------------------------------------------------------------- spike-to-halt (second half of the metric)
 def measure_spike_to_halt(engine, batch, history, steps_needed=10):
-    """Inject (a) a NaN gradient and (b) a x50 loss spike into one optimizer step each — through the
-    same FaultPlan hooks the recovery drills use — and time how long it takes until the training loop
-    holds a halt/rollback decision from LossSpikeMonitor + HaltPolicy. Clocks start when the offending
-    backward pass has finished on the device (the first moment the fault is observable in gradient
-    memory); ``from_forward_end`` additionally counts that backward pass (the loss value exists as soon
-    as the forward ends, but the engine reads it with the step's other by-products to avoid a mid-step
-    sync). Not part of any timed throughput region. Returns milliseconds on this rank."""
+    """Inject three faults into one optimizer step each — through the FaultPlan hooks the recovery drills use — and
+    time how long it takes until the training loop holds a halt/rollback decision from LossSpikeMonitor + HaltPolicy:
+
+    * ``nan_grad``        NaN written into gradient memory after the backward pass
+    * ``nan_grad_mid``    NaN written into the gradient bucket of the middle unit *while backward is still running*,
+                          just before that unit is reduced (where the fused reduce kernel sees it first)
+    * ``loss_spike_x50``  the loss (and every gradient) multiplied by 50
+
+    Three clocks per fault, all ending when the decision is in hand on the host:
+    ``from_fault_written``  device timestamp (CUDA event) right behind the poisoning write -> decision; for the
+                            mid-backward fault this contains the rest of the backward pass, which has to finish before
+                            any optimizer can act; no host synchronisation is inserted anywhere in that step
+    ``from_backward_end``   host clock taken after a device synchronisation at the end of backward -> decision (the
+                            step's control all-reduce, clip/Adam launch, 20-byte pinned read, monitor and policy)
+    ``from_forward_end``    the same from the end of the forward pass (when the loss value first exists)
+    Not part of any timed throughput region. Returns milliseconds on this rank."""
     import torch
     from distributed_llm_training_gpu_manager_b200.ai_engine.loss_monitor import HaltPolicy, LossSpikeMonitor
     from distributed_llm_training_gpu_manager_b200.engine.faults import FaultPlan
 
     mon, policy = LossSpikeMonitor(), HaltPolicy()
     ids, lab = batch
+    on_cuda = torch.cuda.is_available() and getattr(engine, "on_cuda", False)
     while len(history) < steps_needed:              # the spike detector needs a 10-step window
         engine.backward(engine(ids, lab))
         history.append(engine.step()["loss"])
@@ -84,13 +103,27 @@ def measure_spike_to_halt(engine, batch, history, steps_needed=10):
         mon.ingest_device_flags(step=i + 1, loss=loss, nonfinite_grads=False, grad_norm_sq=1.0, learning_rate=0.0)
     base = len(history)
     res = {}
+
     def _sync():
-        if torch.cuda.is_available():
+        if on_cuda:
             torch.cuda.synchronize()
 
-    for k, name in enumerate(("nan_grad", "loss_spike_x50")):
+    n_units = len(engine.layout.units)
+    for k, name in enumerate(("nan_grad", "nan_grad_mid", "loss_spike_x50")):
         nxt = engine.global_steps + 1
-        plan = FaultPlan(nan_grad_at=nxt) if name == "nan_grad" else FaultPlan(spike_at=nxt, spike_factor=50.0)
+        mark = {}
+
+        def stamp(_eng, _m=mark):
+            if on_cuda:
+                _m["evt"] = torch.cuda.Event(enable_timing=True)
+                _m["evt"].record()
+            _m["t"] = time.perf_counter()
+        if name == "nan_grad":
+            plan = FaultPlan(nan_grad_at=nxt)
+        elif name == "nan_grad_mid":
+            plan = FaultPlan(nan_grad_at=nxt, nan_grad_unit=max(1, n_units // 2) if n_units > 1 else 0, on_inject=stamp)
+        else:
+            plan = FaultPlan(spike_at=nxt, spike_factor=50.0)
         plan.install(engine)
         try:
             _sync()
@@ -98,18 +131,27 @@ def measure_spike_to_halt(engine, batch, history, steps_needed=10):
             _sync()
             t_fwd = time.perf_counter()
             engine.backward(loss)
-            _sync()
+            if name != "nan_grad_mid":
+                _sync()                                   # the mid-backward case runs the whole step without a host sync
             t_bwd = time.perf_counter()
             m = engine.step()
             alerts = mon.ingest_device_flags(step=base + k + 1, loss=m["loss"], nonfinite_grads=bool(m["nonfinite"]),
                                              grad_norm_sq=m["grad_norm_sq"], learning_rate=m["lr"])
             action = policy.decide(alerts, 0)
             t_dec = time.perf_counter()
+            from_fault = None
+            if "evt" in mark:
+                end = torch.cuda.Event(enable_timing=True)
+                end.record()                              # the stream is idle here (step() just synchronised it)
+                end.synchronize()
+                from_fault = mark["evt"].elapsed_time(end)
+            elif "t" in mark:
+                from_fault = (t_dec - mark["t"]) * 1e3
         finally:
-            engine.fault_hooks.pop("pre_backward", None)
-            engine.fault_hooks.pop("post_backward", None)
+            plan.uninstall(engine)
         res[name] = {"from_backward_end": (t_dec - t_bwd) * 1e3, "from_forward_end": (t_dec - t_fwd) * 1e3,
-                     "action": action.value, "alerts": [a.alert_type + "/" + a.severity.value for a in alerts]}
+                     "from_fault_written": from_fault, "action": action.value,
+                     "alerts": [a.alert_type + "/" + a.severity.value for a in alerts]}
     return res
 
 
@@ -233,13 +275,18 @@ def supervise(args, argv) -> int:
     except OSError:
         pass
     base_port = int(os.environ.get("MASTER_PORT", "29500"))
-    startup_s = float(os.environ.get("B200ZERO_BENCH_STARTUP_S", "360"))
-    quiet_s = float(os.environ.get("B200ZERO_BENCH_QUIET_S", str(150 + 6 * (args.steps + args.warmup))))
+    # Time limits. The caller allows one run of this script a fixed wall time; the primary attempt and the NCCL re-run
+    # together must fit into `budget_s`, so the primary attempt is cut at 55 % of it however it is (not) progressing.
+    t_begin = time.time()
+    budget_s = float(os.environ.get("B200ZERO_BENCH_BUDGET_S", "800"))
+    startup_s = float(os.environ.get("B200ZERO_BENCH_STARTUP_S", "200"))      # no progress mark / stuck in rendezvous
+    quiet_s = float(os.environ.get("B200ZERO_BENCH_QUIET_S", str(75 + args.steps)))   # between two marks once steps run
     sign = 1 if base_port + 227 < 65000 else -1             # stay inside the valid port range
     attempts = [("primary", list(argv), base_port + sign * 113)]
     if args.comm != "nccl" and args.impl != "nccl":
         attempts.append(("nccl-fallback", list(argv) + ["--comm", "nccl", "--fallback-note",
-                         "the default (fused-collective) run made no progress or failed; re-run on NCCL collectives"],
+                         "the default (fused-collective) run made no progress or failed; this line was measured on NCCL "
+                         "collectives with the same compute kernels"],
                          base_port + sign * 227))
     child = {"p": None}
 
@@ -261,6 +308,8 @@ def supervise(args, argv) -> int:
         env = dict(os.environ, MASTER_PORT=str(port), B200ZERO_HEARTBEAT_FILE=hb, B200ZERO_BENCH_RESULT_FILE=park)
         env.pop("TORCHELASTIC_USE_AGENT_STORE", None)      # the children rendezvous on their own store
         t0 = time.time()
+        last_attempt = name == attempts[-1][0]
+        cutoff = t_begin + (budget_s if last_attempt else 0.55 * budget_s)
         p = child["p"] = subprocess.Popen([sys.executable, os.path.abspath(__file__), "--worker"] + av, env=env)
         verdict = None
         while verdict is None:
@@ -272,6 +321,9 @@ def supervise(args, argv) -> int:
                 pass
             tag, mtime = _read_beat(hb)
             now = time.time()
+            if now > cutoff and tag not in ("done", "printed", "probe"):
+                verdict = "over-budget"
+                break
             if tag in ("done", "printed"):
                 if now - mtime > 45:                        # line printed, teardown stuck: that is a finished run
                     verdict, rc = "done-stuck", 0
@@ -319,7 +371,18 @@ def supervise(args, argv) -> int:
     return rc
 
 
-# --------------------------------------------------------------------------- our arm
+def _attention_used(args) -> str:
+    """Which attention implementation actually served the forward calls of this process."""
+    if args.impl == "torch":
+        return "torch SDPA (library)"
+    from distributed_llm_training_gpu_manager_b200.ops import attention as A
+    used = [k for k, v in A.backend_calls.items() if v]
+    if used == ["native"]:
+        return "native tcgen05 flash attention"
+    return "+".join(used) if used else (args.attn or "module (torch SDPA inside the nn.Module)")
+
+
+# --------------------------------------------------------------------------- our arm / library arm (same harness)
 def run_ours(args) -> int:
     import torch
     import torch.distributed as dist
@@ -328,19 +391,28 @@ def run_ours(args) -> int:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     beat("start")
-    if not torch.cuda.is_available():
+    # B200ZERO_BENCH_CPU=1: self-test of this harness on a machine without a GPU (tiny models, gloo); its line says so
+    # in "data" and is not a benchmark value
+    cpu_selftest = not torch.cuda.is_available() and os.environ.get("B200ZERO_BENCH_CPU") == "1"
+    if not torch.cuda.is_available() and not cpu_selftest:
         if rank == 0:
             print(json.dumps({"metric": METRIC, "value": None, "error": "no CUDA device", "n_gpus": args.gpus}))
         return 1
-    torch.cuda.set_device(local)
-    device = torch.device("cuda", local)
-    if world > 1:
+    on_cuda = not cpu_selftest
+    if on_cuda:
+        torch.cuda.set_device(local)
+    device = torch.device("cuda", local) if on_cuda else torch.device("cpu")
+    if world > 1 or (args.impl == "torch"):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if args.comm != "nccl" and args.impl != "nccl":
-            # our arm uses NCCL for bootstrap and 16-byte control messages only: skip its NVLS (multicast) set-up,
+        os.environ.setdefault("MASTER_PORT", "29517")
+        if args.comm != "nccl" and args.impl not in ("nccl", "torch"):
+            # our arm uses NCCL for bootstrap and 20-byte control messages only: skip its NVLS set-up,
             # which costs seconds at 8 ranks and depends on fabric state left behind by earlier jobs
             os.environ.setdefault("NCCL_NVLS_ENABLE", "0")
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+        if on_cuda:
+            dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+        else:
+            dist.init_process_group("gloo", rank=rank, world_size=world)
     beat("pg")
 
     from distributed_llm_training_gpu_manager_b200.ai_engine import (DeepSpeedConfig, DeepSpeedLauncher,
@@ -355,16 +427,29 @@ def run_ours(args) -> int:
     # (8B fits in 180 GB HBM3e per GPU even unsharded), clipping 1.0, WarmupDecayLR.
     ds_cfg = DeepSpeedConfig(model_name=args.model, zero_stage=ZeROStage(args.zero_stage),
                              offload_optimizer=OffloadDevice.NONE, offload_param=OffloadDevice.NONE,
-                             bf16_enabled=True, fp16_enabled=False, communication_data_type="bf16",
+                             bf16_enabled=on_cuda, fp16_enabled=False, communication_data_type="bf16" if on_cuda else "fp32",
                              train_micro_batch_size_per_gpu=MB, gradient_accumulation_steps=1,
                              num_gpus=world, wall_clock_breakdown=False)
     ds_json = DeepSpeedLauncher().generate_config(ds_cfg)
     comm = args.comm
     if args.impl == "nccl":
         comm = "nccl"
-    use_native = args.engine == "native" or (args.engine == "auto" and mcfg.family == "llama")
-    if use_native:
-        engine = NativeLlamaEngine(mcfg, ds_json, seq_len=S, device=device, comm=comm, attn_backend=args.attn)
+    use_native = args.impl != "torch" and (args.engine == "native" or (args.engine == "auto" and mcfg.family == "llama"))
+    # same work at every N: the activation policy is an input of the run, not a function of free memory
+    recompute = args.recompute or ("none" if args.model == "llama3-8b" and not args.layers else "auto")
+    if args.impl == "torch":
+        # library stand-in for the reference's DeepSpeed job: none of our engine, models or kernels below this line
+        from baseline.torch_zero3 import TorchZero3
+        opt = ds_json["optimizer"]["params"]
+        engine = TorchZero3(mcfg, seq_len=S, micro_batch=MB, device=device, lr=opt["lr"], weight_decay=opt["weight_decay"],
+                            grad_clip=ds_json.get("gradient_clipping", 1.0),
+                            checkpoint_blocks={"none": False, "full": True}.get(args.recompute))
+    elif use_native:
+        # the tcgen05 attention kernel is named explicitly when the shape is in its range, so a library that lacks it
+        # fails the run instead of falling back to SDPA
+        attn = args.attn or ("native" if (mcfg.head_dim == 128 and S % 128 == 0) else None)
+        engine = NativeLlamaEngine(mcfg, ds_json, seq_len=S, device=device, comm=comm, attn_backend=attn,
+                                   recompute=recompute)
     else:
         # generic nn.Module path (BASELINE.json config 2: GPT-2 XL ZeRO-2): torch ops for the model body,
         # our ZeRO engine + fused collectives + fused optimizer around it
@@ -382,14 +467,23 @@ def run_ours(args) -> int:
     # synthetic data: a pool of pinned host batches (e2e) and device-resident copies (device-timed)
     g = torch.Generator().manual_seed(1234 + rank)
     n_pool = 4
-    host = [(torch.randint(0, mcfg.vocab_size, (MB, S), generator=g).pin_memory(),
-             torch.randint(0, mcfg.vocab_size, (MB, S), generator=g).pin_memory()) for _ in range(n_pool)]
+    pin = (lambda t: t.pin_memory()) if on_cuda else (lambda t: t)
+    host = [(pin(torch.randint(0, mcfg.vocab_size, (MB, S), generator=g)),
+             pin(torch.randint(0, mcfg.vocab_size, (MB, S), generator=g))) for _ in range(n_pool)]
     dev = [(a.to(device), b.to(device)) for a, b in host]
 
     def sync_all():
         if world > 1:
             dist.barrier()
-        torch.cuda.synchronize()
+        if on_cuda:
+            torch.cuda.synchronize()
+
+    class _HostEvent:                      # CPU self-test only
+        def record(self):
+            self.t = time.perf_counter()
+
+        def elapsed_time(self, other):
+            return (other.t - self.t) * 1e3
 
     # ---- warm-up ----
     beat("engine")
@@ -403,9 +497,11 @@ def run_ours(args) -> int:
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = bzlib.launches()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0, e1 = ((torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) if on_cuda
+              else (_HostEvent(), _HostEvent()))
     sync_all()
-    torch.cuda.profiler.start()      # lets `ncu --profile-from-start off` skip model construction
+    if on_cuda:
+        torch.cuda.profiler.start()      # lets `ncu --profile-from-start off` skip model construction
     e0.record()
     last = None
     for i in range(args.steps):
@@ -413,7 +509,8 @@ def run_ours(args) -> int:
         loss_hist.append(last["loss"])               # already a host float (step() reads the stats vector)
     e1.record()
     sync_all()
-    torch.cuda.profiler.stop()
+    if on_cuda:
+        torch.cuda.profiler.stop()
     ms_total = e0.elapsed_time(e1)
     beat("timed")
     launches = bzlib.launches() - launches0
@@ -422,7 +519,9 @@ def run_ours(args) -> int:
     # ---- end-to-end region: pinned H2D inputs + D2H loss read every step, wall clock ----
     e2e_ms = None
     h2d = sum(t.numel() * t.element_size() for t in host[0])
-    d2h = 16  # the 4-float stats vector (Σ‖g‖², flag, loss, ‖g‖) read by engine.step()
+    # what the step reads back: ours — the 5-float stats vector (Σ‖g‖², flag, loss, ‖g‖, stop votes) read by
+    # engine.step(); library arm — loss and gradient norm
+    d2h = 8 if args.impl == "torch" else 4 * int(getattr(engine, "_stats_host", torch.zeros(5)).numel())
     if not args.skip_e2e:
         sync_all()
         t0 = time.perf_counter()
@@ -436,7 +535,7 @@ def run_ours(args) -> int:
         e2e_ms = (time.perf_counter() - t0) * 1e3
 
     breakdown = None
-    if args.breakdown:
+    if args.breakdown and args.impl != "torch":
         engine.timers.enabled = True
         engine.cfg.wall_clock_breakdown = True
         sync_all()
@@ -475,19 +574,20 @@ def run_ours(args) -> int:
         "metric": METRIC if (args.model == "llama3-8b" and args.zero_stage == 3) else
         f"{args.model} ZeRO-{args.zero_stage} tokens/s (max over ranks)", "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_total / args.steps, 2), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-        "data": "synthetic tokens, random-init weights",
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if on_cuda else "fp32",
+        "data": "synthetic tokens, random-init weights" + ("" if on_cuda else " [CPU SELF-TEST OF THE HARNESS: not a benchmark value]"),
         "config": {"model": args.model + (f"[TRUNCATED to {args.layers} layers: profiling only]" if args.layers else ""),
                    "global_batch": MB * world, "seq_len": S,
                    "parallelism": f"zero{args.zero_stage}-dp{world}", "micro_batch_per_gpu": MB, "optimizer": "AdamW fp32 master",
                    "grad_clip": 1.0, "activation_recompute": engine.recompute, "comm": engine.comm_mode,
-                   "attention": args.attn or "auto",
+                   "attention": _attention_used(args),
                    "l2": "working set (16 GB weights + 96 GB optimizer state) >> 126 MB L2; no flush needed"},
-        "clocks": clocks, "gpu_launches": launches, "impl": args.impl,
+        "clocks": clocks, "gpu_launches": launches,
+        "impl": "ours-nccl-fallback" if args.fallback_note else args.impl,
         "model_tflops_per_gpu": round(per_gpu_tflops, 1),
         "mfu_vs_measured_cublas_sustained": round(per_gpu_tflops / peaks.get("bf16_tflops_sustained", 1358.3), 3),
         "final_loss": last["loss"] if last else None,
-        "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 1),
+        "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 1) if on_cuda else None,
     }
     if world > 1:
         out["config"]["nccl_nvls"] = os.environ.get("NCCL_NVLS_ENABLE", "default")
@@ -505,7 +605,10 @@ def run_ours(args) -> int:
                       "ms_per_step": round(e2e_total / args.steps, 2)}
     # ---- spike-to-halt: after every timed region. The throughput result is parked first, so a probe that
     #      stalls or fails costs only its own key (the supervising parent prints the parked line). ----
-    if not args.skip_halt:
+    if args.impl == "torch":
+        out["spike_to_halt_ms"] = {"unavailable": "the library arm has no monitor / halt path (neither has the reference: "
+                                                  "its monitor only returns alert objects)"}
+    elif not args.skip_halt:
         park = os.environ.get("B200ZERO_BENCH_RESULT_FILE")
         if park and rank == 0:
             try:
@@ -514,25 +617,41 @@ def run_ours(args) -> int:
             except OSError:
                 pass
         beat("probe")
-        halt, halt_ms = None, [0.0, 0.0, 0.0]
+        faults = ("nan_grad", "nan_grad_mid", "loss_spike_x50")
+        clocks3 = ("from_fault_written", "from_backward_end", "from_forward_end")
+        halt, halt_ms = None, [0.0] * 9
         try:
             sync_all()
             halt = measure_spike_to_halt(engine, dev[0], [x for x in loss_hist if x == x])
-            halt_ms = [halt["nan_grad"]["from_backward_end"], halt["loss_spike_x50"]["from_backward_end"],
-                       halt["loss_spike_x50"]["from_forward_end"]]
+            halt_ms = [float(halt[f][c] or 0.0) for f in faults for c in clocks3]
         except Exception as exc:  # noqa: BLE001
             halt = {"error": f"{type(exc).__name__}: {exc}"}
         t = torch.tensor(halt_ms, device=device, dtype=torch.float64)
+        per_rank = [t.clone() for _ in range(world)]
         if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_gather(per_rank, t)
         if "error" not in halt:
-            halt = {"nan_grad_ms": round(float(t[0]), 3), "loss_spike_x50_ms": round(float(t[1]), 3),
-                    "loss_spike_x50_from_forward_end_ms": round(float(t[2]), 2),
-                    "actions": {"nan_grad": halt["nan_grad"]["action"], "loss_spike_x50": halt["loss_spike_x50"]["action"]},
-                    "alerts": {"nan_grad": halt["nan_grad"]["alerts"], "loss_spike_x50": halt["loss_spike_x50"]["alerts"]},
-                    "definition": "max over ranks; device-synchronised end of the offending backward pass -> halt/rollback "
-                                  "decision in hand (stats all-reduce + pinned D2H + LossSpikeMonitor + HaltPolicy); the "
-                                  "parameter update of a non-finite step is skipped on the device inside that same step"}
+            mx = torch.stack(per_rank).max(0).values.tolist()
+            rep = {"actions": {f: halt[f]["action"] for f in faults}, "alerts": {f: halt[f]["alerts"] for f in faults}}
+            for i, f in enumerate(faults):
+                rep[f] = {c: round(mx[3 * i + j], 3) for j, c in enumerate(clocks3)}
+                rep[f]["per_rank_from_backward_end"] = [round(float(r[3 * i + 1]), 3) for r in per_rank]
+            rep["nan_grad_mid"].pop("from_backward_end")       # no host sync in that step: only the device clock counts
+            rep["nan_grad_mid"].pop("per_rank_from_backward_end")
+            rep["nan_grad_mid"]["per_rank_from_fault_written"] = [round(float(r[3]), 3) for r in per_rank]
+            rep["nan_grad"].pop("from_fault_written")          # that fault is written at the end of backward
+            rep["loss_spike_x50"].pop("from_fault_written")    # the spike exists from the end of forward
+            # headline keys (kept from earlier rounds): end of the offending backward pass -> decision
+            rep["nan_grad_ms"] = rep["nan_grad"]["from_backward_end"]
+            rep["loss_spike_x50_ms"] = rep["loss_spike_x50"]["from_backward_end"]
+            rep["definition"] = ("milliseconds until the halt/rollback decision is in hand on the host, max over ranks. "
+                                 "from_fault_written: CUDA-event timestamp right behind the poisoning write, taken while "
+                                 "backward is still running, no host sync in that step (contains the rest of backward); "
+                                 "from_backward_end: host clock after a device sync at the end of the offending backward "
+                                 "(control all-reduce + clip/Adam launch + 20-byte pinned read + LossSpikeMonitor + "
+                                 "HaltPolicy); from_forward_end: the same from the end of forward. The parameter update of "
+                                 "a non-finite step is skipped on the device inside that same step")
+            halt = rep
         out["spike_to_halt_ms"] = halt
     if rank == 0:
         print(json.dumps(out), flush=True)

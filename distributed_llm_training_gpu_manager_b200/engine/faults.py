@@ -13,7 +13,7 @@ from __future__ import annotations
 import os
 import signal
 from dataclasses import dataclass, field
-from typing import Optional, Set
+from typing import Callable, Optional, Set
 
 
 @dataclass
@@ -21,9 +21,11 @@ class FaultPlan:
     spike_at: Optional[int] = None
     spike_factor: float = 50.0
     nan_grad_at: Optional[int] = None
+    nan_grad_unit: Optional[int] = None     # poison that unit's gradient bucket just before it is reduced (mid-backward)
     kill_at: Optional[int] = None
     kill_rank: int = 0
     preempt_at: Optional[int] = None
+    on_inject: Optional[Callable] = None    # called right after a mid-backward fault was written (probes timestamp it)
     fired: Set[str] = field(default_factory=set)
 
     @classmethod
@@ -60,15 +62,29 @@ class FaultPlan:
                 return loss * plan.spike_factor
             return loss
 
+        def pre_reduce(eng, ui):
+            # a fault that appears while the backward pass is still running: the NaN sits in the unit's gradient
+            # bucket when its reduce-scatter starts, so the reduce kernels (or the norm pass) flag it themselves
+            step = eng.global_steps + 1
+            if plan.nan_grad_at == step and plan.nan_grad_unit == ui and plan._once(f"nan{step}"):
+                eng._unit_gbuf[ui][:1] = float("nan")
+                if plan.on_inject is not None:
+                    plan.on_inject(eng)
+
         def post_backward(eng):
             step = eng.global_steps + 1
-            if plan.nan_grad_at == step and plan._once(f"nan{step}"):
+            if plan.nan_grad_at == step and plan.nan_grad_unit is None and plan._once(f"nan{step}"):
                 eng.shard_grads[0] = float("nan")
                 if getattr(eng, "fused", None) is not None:   # the fused path derives the flag inside its reduce kernels
                     eng._flag.fill_(1)
 
         engine.fault_hooks["pre_backward"] = pre_backward
         engine.fault_hooks["post_backward"] = post_backward
+        engine.fault_hooks["pre_reduce"] = pre_reduce
+
+    def uninstall(self, engine) -> None:
+        for k in ("pre_backward", "post_backward", "pre_reduce"):
+            engine.fault_hooks.pop(k, None)
 
     def at_step_start(self, engine) -> None:
         step = engine.global_steps + 1

@@ -445,6 +445,9 @@ class ZeroEngine:
         if self._reduced[ui]:
             return
         self._reduced[ui] = True
+        hook = self.fault_hooks.get("pre_reduce")
+        if hook is not None:
+            hook(self, ui)
         if self._grads_alias:
             return                      # single rank: the unit's gradients already live in the shard
         u = self.layout.units[ui]

@@ -11,6 +11,7 @@ The reference has no attention code (it ships no model).
 """
 from __future__ import annotations
 
+import logging
 import os
 from typing import Any, Optional, Tuple
 
@@ -20,6 +21,11 @@ import torch.nn.functional as F
 from . import lib as _lib
 
 _BACKEND = os.environ.get("B200ZERO_ATTN", "auto")
+_log = logging.getLogger(__name__)
+# how many forward calls each backend served in this process (bench.py reports it, so a library fallback on a GPU
+# box is visible in the result line instead of hiding behind "auto")
+backend_calls = {"native": 0, "sdpa": 0}
+_warned = set()
 
 
 def native_available() -> bool:
@@ -53,6 +59,12 @@ def attention_fwd(qkv: torch.Tensor, B: int, S: int, Hq: int, Hk: int, hd: int,
     backend = backend or _BACKEND
     if backend == "auto":
         backend = "native" if (qkv.is_cuda and native_available() and hd == 128 and S % 128 == 0) else "sdpa"
+        if backend == "sdpa" and qkv.is_cuda and (S, hd) not in _warned:
+            _warned.add((S, hd))
+            why = ("kernel library has no flash-attention entry points" if not native_available() else
+                   f"shape outside the tcgen05 kernel's range (head_dim={hd}, seq={S}; needs head_dim 128, seq % 128 == 0)")
+            _log.warning("attention: using torch SDPA on a GPU instead of the native kernel: %s", why)
+    backend_calls[backend] = backend_calls.get(backend, 0) + 1
     if backend == "native":
         from .flash import flash_fwd
         out, lse = flash_fwd(qkv, B, S, Hq, Hk, hd)
