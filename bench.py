@@ -622,7 +622,9 @@ def run_ours(args) -> int:
         halt, halt_ms = None, [0.0] * 9
         try:
             sync_all()
-            halt = measure_spike_to_halt(engine, dev[0], [x for x in loss_hist if x == x])
+            # the monitor is primed with the most recent window only: losses from the first warm-up steps (random-init
+            # weights) are an order of magnitude above the current level and would hide a x50 spike of a small loss
+            halt = measure_spike_to_halt(engine, dev[0], [x for x in loss_hist if x == x][-10:])
             halt_ms = [float(halt[f][c] or 0.0) for f in faults for c in clocks3]
         except Exception as exc:  # noqa: BLE001
             halt = {"error": f"{type(exc).__name__}: {exc}"}

@@ -398,7 +398,7 @@ def load_checkpoint(engine, load_dir: str, tag: Optional[str] = None, verify: bo
         dist.barrier()
     if engine.stage >= 3 and engine.pooled_params:
         engine._resident = [False] * len(engine.layout.units)
-        engine._slot_owner = [None, None]
+        engine._slot_owner = [None] * engine._n_pslots
         engine._gather_unit(0)
     else:
         for ui in range(len(engine.layout.units)):

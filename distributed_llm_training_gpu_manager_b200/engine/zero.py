@@ -280,6 +280,7 @@ class ZeroEngine:
         self.shard_params.copy_(self.master.to(dev, non_blocking=False).to(cd))
         # parameter / gradient buffers
         nblk = len(L.units) - 1
+        self._n_pslots = 2
         # One rank: nothing to gather or reduce — parameters and gradients *are* the shard buffers
         # (per unit, the shard layout of replicated tensors equals the unit's full layout).
         self._single = self.world_size == 1 and L.part_numel == 0
@@ -287,14 +288,21 @@ class ZeroEngine:
         if self._single:
             self._unit_pbuf = [self.shard_params[u.repl_shard_start:u.repl_shard_end] for u in L.units]
             self._resident = [True] * len(L.units)
-            self._slot_owner = [None, None]
+            self._slot_owner = [None] * self._n_pslots
         elif self.stage >= 3 and nblk >= 2:
             blk_numel = max(u.full_numel for u in L.units[1:])
+            # stage3_max_live_parameters (ref deepspeed_launcher.py:188) bounds how many gathered blocks stay alive:
+            # at least the two the prefetch pipeline needs, at most all of them. Blocks still alive when backward
+            # turns around (stage3_max_reuse_distance, :189: reuse is that close) are not gathered a second time.
+            self._n_pslots = max(2, min(nblk, cfg.max_live_parameters // max(blk_numel, 1)))
+            if cfg.max_reuse_distance < blk_numel:
+                self._n_pslots = 2               # nothing is worth keeping beyond the pipeline's own two buffers
+            self._n_pslots = int(os.environ.get("B200ZERO_PARAM_SLOTS", self._n_pslots))
             self._pbuf_root = torch.zeros(L.units[0].full_numel, dtype=cd, device=dev)
-            self._pbuf_blk = [torch.zeros(blk_numel, dtype=cd, device=dev) for _ in range(2)]
-            self._unit_pbuf = [self._pbuf_root] + [self._pbuf_blk[(i - 1) % 2] for i in range(1, len(L.units))]
+            self._pbuf_blk = [torch.zeros(blk_numel, dtype=cd, device=dev) for _ in range(self._n_pslots)]
+            self._unit_pbuf = [self._pbuf_root] + [self._pbuf_blk[self._pslot(i)] for i in range(1, len(L.units))]
             self._resident = [False] * len(L.units)      # which unit's weights currently sit in its buffer
-            self._slot_owner: List[Optional[int]] = [None, None]
+            self._slot_owner: List[Optional[int]] = [None] * self._n_pslots
         else:
             total = sum(u.full_numel for u in L.units)
             self._pbuf_all = self._zeros(total, cd, "pbuf_all", symmetric=True)
@@ -303,7 +311,7 @@ class ZeroEngine:
                 self._unit_pbuf.append(self._pbuf_all[off:off + u.full_numel])
                 off += u.full_numel
             self._resident = [True] * len(L.units)
-            self._slot_owner = [None, None]
+            self._slot_owner = [None] * self._n_pslots
         self.pooled_params = self.stage >= 3 and nblk >= 2 and not self._single
         self.pooled_grads = self.stage >= 2 and nblk >= 2 and not alias_grads
         self._grads_alias = alias_grads
@@ -392,6 +400,10 @@ class ZeroEngine:
         return hook
 
     # ------------------------------------------------------------------ stage-3 parameter residency
+    def _pslot(self, ui: int) -> int:
+        """Which of the gathered-block buffers unit ``ui`` (>= 1) lives in."""
+        return (ui - 1) % self._n_pslots
+
     def _gather_unit(self, ui: int, stream=None) -> None:
         """All-gather unit ``ui``'s rows into its buffer (X2). Replicated tensors are local copies."""
         if self._single:
@@ -412,14 +424,14 @@ class ZeroEngine:
                         dst.copy_(src)
         self._resident[ui] = True
         if ui >= 1 and self.pooled_params:
-            slot = (ui - 1) % 2
+            slot = self._pslot(ui)
             prev = self._slot_owner[slot]
             if prev is not None and prev != ui:
                 self._resident[prev] = False
             self._slot_owner[slot] = ui
 
     def _ensure_resident(self, ui: int) -> None:
-        if self._resident[ui] and (ui == 0 or self._slot_owner[(ui - 1) % 2] == ui):
+        if self._resident[ui] and (ui == 0 or self._slot_owner[self._pslot(ui)] == ui):
             evt = self._prefetch_evt.pop(ui, None)
             if evt is not None:
                 torch.cuda.current_stream().wait_event(evt)
@@ -428,7 +440,7 @@ class ZeroEngine:
 
     def _prefetch(self, ui: int) -> None:
         """Issue the gather of unit ``ui`` on the comm stream (``stage3_prefetch_bucket_size`` > 0)."""
-        if self._resident[ui] and self._slot_owner[(ui - 1) % 2] == ui:
+        if self._resident[ui] and self._slot_owner[self._pslot(ui)] == ui:
             return
         if not self.on_cuda or not self.cfg.overlap_comm or self.cfg.prefetch_bucket_size <= 0:
             return  # gathered synchronously on demand
@@ -616,7 +628,7 @@ class ZeroEngine:
             with self.timers.phase("allgather"):
                 if self.stage >= 3 and self.pooled_params:
                     self._resident = [False] * len(L.units)
-                    self._slot_owner = [None, None]
+                    self._slot_owner = [None] * self._n_pslots
                     self._gather_unit(0)
                 elif self.fused is not None:
                     pass                        # rows were pushed into every rank's buffers by the Adam kernel
@@ -758,7 +770,7 @@ class ZeroEngine:
             dist.barrier()
         if self.stage >= 3 and self.pooled_params:
             self._resident = [False] * len(self.layout.units)
-            self._slot_owner = [None, None]
+            self._slot_owner = [None] * self._n_pslots
             self._gather_unit(0)
         else:
             for ui in range(len(self.layout.units)):

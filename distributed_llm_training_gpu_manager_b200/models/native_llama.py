@@ -242,7 +242,7 @@ class NativeLlamaEngine(ZeroEngine):
         return self.grad_view(f"blocks.{layer}.{name}.weight")
 
     def _unit_is_resident(self, ui: int) -> bool:
-        return self._resident[ui] and (ui == 0 or self._slot_owner[(ui - 1) % 2] == ui)
+        return self._resident[ui] and (ui == 0 or self._slot_owner[self._pslot(ui)] == ui)
 
     def _linear(self, l: int, name: str, x: torch.Tensor, ag: bool) -> torch.Tensor:
         """y = x · Wᵀ; when ``ag`` the weight is all-gathered inside the GEMM kernel (K2) and left in
@@ -292,7 +292,7 @@ class NativeLlamaEngine(ZeroEngine):
             if not spec.partitioned:
                 pb[spec.full_offset:spec.full_offset + spec.numel].copy_(
                     self.shard_params[spec.shard_offset:spec.shard_offset + spec.shard_numel])
-        slot = (ui - 1) % 2
+        slot = self._pslot(ui)
         prev = self._slot_owner[slot]
         if prev is not None and prev != ui:
             self._resident[prev] = False

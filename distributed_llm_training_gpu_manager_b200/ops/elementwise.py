@@ -42,16 +42,18 @@ _lib.register("bz_swiglu_bwd_v2", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib.i64
 
 
 def _swiglu_version() -> int:
-    """2 = the division-free SwiGLU kernels of csrc/elementwise_v2.cu (bit-identical to v1), 3 = the same with
-    rcp.approx in the sigmoid (opt-in until validated on hardware)."""
+    """1 = csrc/elementwise.cu; 2 = the division-free kernels of csrc/elementwise_v2.cu (bit-identical to 1);
+    3 (default) = the same with rcp.approx in the sigmoid. Measured on B200 at [8192, 2·14336]: forward
+    303 / 148 / 119 µs, backward 209 / 211 / 193 µs (profiles/kernel_checks_r2.txt)."""
     import os
-    return int(os.environ.get("B200ZERO_SWIGLU", "1"))
+    return int(os.environ.get("B200ZERO_SWIGLU", "3"))
 
 
 def _rmsnorm_version() -> int:
-    """2 = the row-ahead-prefetch kernels of csrc/elementwise_v2.cu (opt-in until validated on hardware)."""
+    """2 (default) = the row-ahead-prefetch kernels of csrc/elementwise_v2.cu, bit-identical to 1
+    (csrc/elementwise.cu); measured on B200 at [8192, 4096]: backward 114 -> 93 µs, forward unchanged."""
     import os
-    return int(os.environ.get("B200ZERO_RMSNORM", "1"))
+    return int(os.environ.get("B200ZERO_RMSNORM", "2"))
 
 
 def rmsnorm_ref(x, w, eps, delta=None):

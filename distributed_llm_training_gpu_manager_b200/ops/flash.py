@@ -19,9 +19,10 @@ _err_flag = {}
 def flash_fwd(qkv: torch.Tensor, B: int, S: int, Hq: int, Hk: int, hd: int,
               want_lse: bool = True, version: Optional[int] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     """Causal GQA attention forward. Returns (out [T, Hq*hd] bf16, lse [Hq, T] fp32).
-    ``version`` (default ``$B200ZERO_FLASH_FWD`` or 2): 3 selects the double-buffered-P kernel of
-    ``csrc/attention_v3.cu`` (opt-in until validated on hardware); 32 / 34 / 38 = the same kernel with every
-    2nd / 4th / 8th exponential evaluated on the FMA pipe instead of the SFU."""
+    ``version`` (default ``$B200ZERO_FLASH_FWD`` or 3): 3 = the double-buffered-P kernel of
+    ``csrc/attention_v3.cu``, 2 = the first kernel (``csrc/attention.cu``); 32 / 34 / 38 = v3 with every
+    2nd / 4th / 8th exponential evaluated on the FMA pipe instead of the SFU. Measured on B200 (B=2, S=4096,
+    32q/8kv, d=128): v2 686, v3 801, 38: 785, 34: 795, 32: 728 TFLOP/s (profiles/kernel_checks_r2.txt)."""
     import os
     T = B * S
     assert qkv.is_contiguous() and qkv.shape == (T, (Hq + 2 * Hk) * hd) and qkv.dtype == torch.bfloat16
@@ -29,7 +30,7 @@ def flash_fwd(qkv: torch.Tensor, B: int, S: int, Hq: int, Hk: int, hd: int,
     lse = torch.empty((Hq, T), dtype=torch.float32, device=qkv.device) if want_lse else None
     L = _lib.load(required=True)
     if version is None:
-        version = int(os.environ.get("B200ZERO_FLASH_FWD", "2"))
+        version = int(os.environ.get("B200ZERO_FLASH_FWD", "3"))
     if version in (3, 32, 34, 38):
         key = str(qkv.device)
         if key not in _err_flag:
@@ -56,7 +57,8 @@ _lib.register("bz_flash_attn_bwd_v3", _lib.i32, [_lib.vp, _lib.vp, _lib.vp, _lib
 def flash_bwd(qkv: torch.Tensor, out: torch.Tensor, lse: torch.Tensor, dout: torch.Tensor, B: int, S: int, Hq: int,
               Hk: int, hd: int, dqkv: Optional[torch.Tensor] = None, version: Optional[int] = None) -> torch.Tensor:
     """Gradient w.r.t. the fused QKV buffer (same layout as ``qkv``). ``version`` (default ``$B200ZERO_FLASH_BWD`` or
-    2): 3 selects the pipelined schedule of ``csrc/attention_bwd_v3.cu`` (opt-in until validated on hardware)."""
+    3): 3 = the pipelined schedule of ``csrc/attention_bwd_v3.cu``, 2 = ``csrc/attention.cu``. Measured on B200 at the
+    shape above: 508 -> 575 TFLOP/s."""
     import os
     T = B * S
     L = _lib.load(required=True)
@@ -68,7 +70,7 @@ def flash_bwd(qkv: torch.Tensor, out: torch.Tensor, lse: torch.Tensor, dout: tor
         _ws[key] = torch.empty(need, dtype=torch.float32, device=qkv.device)
     assert dout.is_contiguous() and out.is_contiguous() and dqkv.is_contiguous()
     if version is None:
-        version = int(os.environ.get("B200ZERO_FLASH_BWD", "2"))
+        version = int(os.environ.get("B200ZERO_FLASH_BWD", "3"))
     if version == 3:
         if key not in _err_flag:
             _err_flag[key] = torch.zeros(1, dtype=torch.int32, device=qkv.device)

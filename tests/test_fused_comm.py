@@ -309,10 +309,9 @@ print("PULL_V2_OK")
 """
 
 
-@pytest.mark.xfail(strict=False, reason="division-free pull all-gather written after this round's GPU budget was spent")
 def test_pull_allgather_v2_matches_v1_emulated():
     """Pure copy kernel without cross-rank waits: ranks are emulated on one GPU; v2 must reproduce v1 byte for byte.
-    Child process: not yet validated on hardware."""
+    Runs in a child process so that a device fault cannot take the rest of the session down."""
     import os
     import subprocess
     import sys

@@ -104,3 +104,42 @@ def test_segment_lengths_are_whole_vectors():
     for a, b in zip(repl, repl[1:]):
         assert a.shard_offset + seg_len(a, 4) <= b.shard_offset
     assert repl[-1].shard_offset + seg_len(repl[-1], 4) <= L.shard_numel
+
+
+# ---------------------------------------------------------------- stage3_max_live_parameters drives the block buffers
+def _slots_rank(rank, world, max_live, reuse):
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.models import get_config
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+    mc = get_config("llama-tiny", n_layers=6)
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+        stage3_max_live_parameters=max_live, stage3_max_reuse_distance=reuse, stage3_param_persistence_threshold=1000,
+        wall_clock_breakdown=False))
+    eng = NativeLlamaEngine(mc, ds, seq_len=32, device=torch.device("cpu"), seed=3)
+    gathers = []
+    real = eng._gather_unit
+
+    def counting(ui, stream=None):
+        gathers.append(ui)
+        return real(ui, stream=stream)
+    eng._gather_unit = counting
+    g = torch.Generator().manual_seed(100 + rank)
+    losses = []
+    for _ in range(3):
+        ids = torch.randint(0, mc.vocab_size, (2, 32), generator=g)
+        losses.append(eng.train_step(ids, ids)["loss"])
+    blk = max(u.full_numel for u in eng.layout.units[1:])
+    return losses, eng._n_pslots, len([u for u in gathers if u >= 1]), blk
+
+
+def test_max_live_parameters_sets_resident_blocks_and_saves_gathers():
+    blk = run_ranks(_slots_rank, 2, (1, 10 ** 9))[0][3]
+    base = run_ranks(_slots_rank, 2, (2 * blk, 10 ** 9))           # room for two blocks: the pipeline's minimum
+    wide = run_ranks(_slots_rank, 2, (4 * blk + 1, 10 ** 9))       # four blocks stay gathered
+    near = run_ranks(_slots_rank, 2, (4 * blk + 1, 1))             # reuse distance too short to keep anything extra
+    assert base[0][1] == 2 and wide[0][1] == 4 and near[0][1] == 2
+    assert wide[0][0] == base[0][0] == near[0][0]                   # same arithmetic, different residency
+    # 6 blocks, 3 steps: every block is gathered for forward; backward re-gathers all but the ones still alive
+    assert base[0][2] == 3 * (6 + 4) and wide[0][2] == 3 * (6 + 2)
