@@ -385,7 +385,7 @@ def load_checkpoint(engine, load_dir: str, tag: Optional[str] = None, verify: bo
     engine.micro_steps = engine.global_steps * engine.cfg.grad_accum
     engine.schedule.load_state_dict(msd.get("lr_scheduler", {}))
     engine.schedule.last_step = engine.global_steps
-    engine.shard_params.copy_(engine.master.to(engine.device).to(engine.compute_dtype))
+    engine._refresh_shard_params()
     engine.shard_grads.zero_()
     for gb in {b.data_ptr(): b for b in engine._unit_gbuf}.values():
         gb.zero_()

@@ -49,15 +49,18 @@ def host_adam_step(engine, lr: float, step_no: int) -> None:
     coef, skip = float(host_vals[0]), bool(host_vals[1] > 0)
     if skip:
         return
+    # sub_group_size (ref deepspeed_launcher.py:194) caps the tile the optimizer works on; below that cap the shard is
+    # cut further so that the copy down, the host update and the copy up of neighbouring tiles overlap
+    CH = max(1 << 16, min(_CHUNK, int(cfg.sub_group_size)))
     if not hasattr(engine, "_off_stream"):
         engine._off_stream = torch.cuda.Stream(device=dev)
         nbuf = 2
         gdt = engine.shard_grads.dtype
-        engine._off_g = [torch.empty(min(_CHUNK, n), dtype=gdt).pin_memory() for _ in range(nbuf)]
-        engine._off_p = [torch.empty(min(_CHUNK, n), dtype=torch.bfloat16).pin_memory() for _ in range(nbuf)]
+        engine._off_g = [torch.empty(min(CH, n), dtype=gdt).pin_memory() for _ in range(nbuf)]
+        engine._off_p = [torch.empty(min(CH, n), dtype=torch.bfloat16).pin_memory() for _ in range(nbuf)]
     side = engine._off_stream
     side.wait_stream(torch.cuda.current_stream())
-    chunks = [(o, min(o + _CHUNK, n)) for o in range(0, n, _CHUNK)]
+    chunks = [(o, min(o + CH, n)) for o in range(0, n, CH)]
     d2h_evt = [None] * len(chunks)
     h2d_evt = [None] * 2
 
@@ -78,12 +81,19 @@ def host_adam_step(engine, lr: float, step_no: int) -> None:
             issue_d2h(i + 1)
         d2h_evt[i].synchronize()
         b = i % 2
-        outp = engine._off_p[b][: hi - lo] if to_bf16 else None
+        to_host_shard = getattr(engine, "param_offload", False)     # parameters live on the host too: no copy back
+        if to_host_shard and to_bf16:
+            outp = engine.shard_params[lo:hi]
+        else:
+            outp = engine._off_p[b][: hi - lo] if to_bf16 else None
         host_adamw(engine.master[lo:hi], engine.exp_avg[lo:hi], engine.exp_avg_sq[lo:hi], engine._off_g[b][: hi - lo],
                    outp, lr=lr, beta1=cfg.betas[0], beta2=cfg.betas[1], eps=cfg.eps, weight_decay=cfg.weight_decay,
                    step=step_no, grad_scale=coef)
         with torch.cuda.stream(side):
-            if to_bf16:
+            if to_host_shard:
+                if not to_bf16:
+                    engine.shard_params[lo:hi].copy_(engine.master[lo:hi].to(engine.compute_dtype))
+            elif to_bf16:
                 engine.shard_params[lo:hi].copy_(outp, non_blocking=True)
             else:
                 engine.shard_params[lo:hi].copy_(engine.master[lo:hi].to(engine.compute_dtype), non_blocking=True)

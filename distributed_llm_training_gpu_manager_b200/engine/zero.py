@@ -30,6 +30,7 @@ Design (see ``partition.py`` for the layout):
 """
 from __future__ import annotations
 
+import logging
 import os
 import time
 from contextlib import contextmanager, nullcontext
@@ -45,6 +46,7 @@ from .partition import Layout, ParamSpec, build_layout
 from .schedules import DynamicLossScaler, LRSchedule
 
 _BLOCK_LIST_NAMES = ("blocks", "layers", "h", "transformer_blocks")
+_log = logging.getLogger(__name__)
 
 
 def _dist_ready() -> bool:
@@ -166,7 +168,13 @@ class ZeroEngine:
         self._want_fused = (comm in ("fused", "auto") and self.on_cuda and self.world_size > 1
                             and self.cfg.compute_dtype == torch.bfloat16
                             and self.cfg.offload_optimizer == "none"     # K3 updates device-resident state
+                            and self.cfg.offload_param == "none"         # K2 / pull gather read device-resident shards
                             and os.environ.get("B200ZERO_COMM", comm) != "nccl")
+        if comm in ("fused", "auto") and self.on_cuda and self.world_size > 1 and not self._want_fused:
+            why = ("compute dtype is not bf16" if self.cfg.compute_dtype != torch.bfloat16 else
+                   "optimizer state is offloaded" if self.cfg.offload_optimizer != "none" else
+                   "parameters are offloaded" if self.cfg.offload_param != "none" else "B200ZERO_COMM=nccl")
+            _log.warning("fused peer-memory collectives declined (%s): this job runs on NCCL collectives", why)
         if self._want_fused and comm == "auto":
             self._want_fused = self._probe_peer_memory()
             if self._want_fused:
@@ -266,7 +274,22 @@ class ZeroEngine:
             self.master, self.exp_avg, self.exp_avg_sq = mk(), mk(), mk()
         self.state_device = state_dev
         self.shard_grads = torch.zeros(L.shard_numel, dtype=cfg.accum_dtype, device=dev)
-        self.shard_params = self._zeros(L.shard_numel, cd, "shard_params", symmetric=self.stage >= 3)
+        # offload_param (ref deepspeed_launcher.py:40,205-212; on in the reference's default config and its 70b preset):
+        # the rank's 16-bit parameter shard lives in pinned host memory; a unit's rows are copied to a small device
+        # staging buffer on the stream that gathers the unit (the prefetch stream when overlap_comm is on), so HBM
+        # holds gathered blocks only. "nvme" is served from the same host tier.
+        self.param_offload = cfg.offload_param in ("cpu", "nvme") and self.stage >= 3 and len(L.units) - 1 >= 2
+        if cfg.offload_param in ("cpu", "nvme") and not self.param_offload:
+            _log.warning("offload_param=%s ignored: it needs ZeRO-3 and a model with at least two blocks", cfg.offload_param)
+        if cfg.offload_param == "nvme" and self.param_offload:
+            _log.warning("offload_param=nvme: parameter shards are kept in pinned host memory (the NVMe tier holds "
+                         "optimizer state only)")
+        if self.param_offload:
+            self.shard_params = torch.zeros(L.shard_numel, dtype=cd, device="cpu",
+                                            pin_memory=self.on_cuda and cfg.pin_memory)
+            self._pstage: Dict[Any, torch.Tensor] = {}
+        else:
+            self.shard_params = self._zeros(L.shard_numel, cd, "shard_params", symmetric=self.stage >= 3)
         # master <- initial fp32 values, own rows only
         for u in L.units:
             for spec in u.params:
@@ -277,13 +300,13 @@ class ZeroEngine:
                     dst.copy_(self.source.init_rows(spec.name, spec.shape, r0, r0 + rows).reshape(-1))
                 else:
                     dst.copy_(self._slice_rows(spec, self._param_of[spec.name].data.detach().float()))
-        self.shard_params.copy_(self.master.to(dev, non_blocking=False).to(cd))
+        self._refresh_shard_params()
         # parameter / gradient buffers
         nblk = len(L.units) - 1
         self._n_pslots = 2
         # One rank: nothing to gather or reduce — parameters and gradients *are* the shard buffers
         # (per unit, the shard layout of replicated tensors equals the unit's full layout).
-        self._single = self.world_size == 1 and L.part_numel == 0
+        self._single = self.world_size == 1 and L.part_numel == 0 and not self.param_offload
         alias_grads = self._single and cfg.accum_dtype == cd
         if self._single:
             self._unit_pbuf = [self.shard_params[u.repl_shard_start:u.repl_shard_end] for u in L.units]
@@ -415,9 +438,13 @@ class ZeroEngine:
             if self.fused is not None and self.fused.gather_unit(ui):
                 pass
             else:
+                shard, base_p, base_r = self.shard_params, 0, 0
+                if self.param_offload:
+                    shard, base_p, base_r = self._stage_unit_shard(ui)
                 for spec in u.params:
                     dst = pb[spec.full_offset:spec.full_offset + spec.numel]
-                    src = self.shard_params[spec.shard_offset:spec.shard_offset + spec.shard_numel]
+                    o = spec.shard_offset - (base_p if spec.partitioned else base_r)
+                    src = shard[o:o + spec.shard_numel]
                     if spec.partitioned:
                         _all_gather(dst, src)
                     else:
@@ -429,6 +456,37 @@ class ZeroEngine:
             if prev is not None and prev != ui:
                 self._resident[prev] = False
             self._slot_owner[slot] = ui
+
+    def _stage_unit_shard(self, ui: int):
+        """Parameter offload: bring unit ``ui``'s rows of the host-resident shard onto the device (two contiguous
+        pinned copies on the current stream: the partitioned range and the replicated range). Returns the staging
+        tensor and the shard offsets its two halves start from."""
+        u = self.layout.units[ui]
+        n_part, n_repl = u.part_shard_end - u.part_shard_start, u.repl_shard_end - u.repl_shard_start
+        key = "root" if ui == 0 else self._pslot(ui)
+        stg = self._pstage.get(key)
+        if stg is None or stg.numel() < n_part + n_repl:
+            stg = torch.empty(n_part + n_repl, dtype=self.compute_dtype, device=self.device)
+            self._pstage[key] = stg
+        if n_part:
+            stg[:n_part].copy_(self.shard_params[u.part_shard_start:u.part_shard_end], non_blocking=True)
+        if n_repl:
+            stg[n_part:n_part + n_repl].copy_(self.shard_params[u.repl_shard_start:u.repl_shard_end], non_blocking=True)
+        self.h2d_param_bytes = getattr(self, "h2d_param_bytes", 0) + (n_part + n_repl) * stg.element_size()
+        # a replicated tensor's offset inside the staging buffer = its shard offset - repl_start + n_part
+        return stg, u.part_shard_start, u.repl_shard_start - n_part
+
+    def _refresh_shard_params(self, lo: int = 0, hi: Optional[int] = None) -> None:
+        """16-bit shard <- fp32 master for elements [lo, hi) (wherever either of them lives), in bounded chunks."""
+        hi = self.layout.shard_numel if hi is None else hi
+        step = 1 << 26
+        for a in range(lo, hi, step):
+            b = min(a + step, hi)
+            src = self.master[a:b]
+            if self.shard_params.is_cuda or not src.is_cuda:
+                self.shard_params[a:b].copy_(src.to(self.shard_params.device).to(self.compute_dtype))
+            else:
+                self.shard_params[a:b].copy_(src.to(self.compute_dtype))       # cast on the device, 2 bytes/elem over PCIe
 
     def _ensure_resident(self, ui: int) -> None:
         if self._resident[ui] and (ui == 0 or self._slot_owner[self._pslot(ui)] == ui):
@@ -605,9 +663,10 @@ class ZeroEngine:
                 O.adamw_step(self.master, self.exp_avg, self.exp_avg_sq, self.shard_grads, lr=lr, beta1=cfg.betas[0],
                              beta2=cfg.betas[1], eps=cfg.eps, weight_decay=cfg.weight_decay, step=step_no,
                              grad_scale_dev=self._coef, skip_flag=self._flag,
-                             param_out=self.shard_params if self.compute_dtype == torch.bfloat16 and self.on_cuda else None)
-                if not (self.compute_dtype == torch.bfloat16 and self.on_cuda):
-                    self.shard_params.copy_(self.master.to(self.compute_dtype))
+                             param_out=self.shard_params if self.compute_dtype == torch.bfloat16 and self.on_cuda
+                             and not self.param_offload else None)
+                if not (self.compute_dtype == torch.bfloat16 and self.on_cuda) or self.param_offload:
+                    self._refresh_shard_params()
             if self.fused is None and self._adam_stream is None:
                 self.shard_grads.zero_()       # (the fused Adam kernel zeroes the shard as it reads it)
             # host read: the one sync of the step (feeds the loss monitor)
@@ -763,7 +822,7 @@ class ZeroEngine:
                 dst.copy_(self._slice_rows(spec, t.detach().to(torch.float32)))
         if strict and missing:
             raise KeyError(f"parameters not supplied: {missing[:8]}{' ...' if len(missing) > 8 else ''}")
-        self.shard_params.copy_(self.master.to(self.device).to(self.compute_dtype))
+        self._refresh_shard_params()
         if _dist_ready() and self.world_size > 1:
             if self.on_cuda:
                 torch.cuda.synchronize(self.device)      # peers read this shard directly in the fused gather

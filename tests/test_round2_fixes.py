@@ -143,3 +143,43 @@ def test_max_live_parameters_sets_resident_blocks_and_saves_gathers():
     assert wide[0][0] == base[0][0] == near[0][0]                   # same arithmetic, different residency
     # 6 blocks, 3 steps: every block is gathered for forward; backward re-gathers all but the ones still alive
     assert base[0][2] == 3 * (6 + 4) and wide[0][2] == 3 * (6 + 2)
+
+
+# ---------------------------------------------------------------- offload_param: host-resident 16-bit shards
+def _poffload_rank(rank, world, offload_param, offload_opt, native):
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.models import get_config
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer=offload_opt, offload_param=offload_param, bf16_enabled=False, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+        stage3_param_persistence_threshold=1000, wall_clock_breakdown=False))
+    if native:
+        mc = get_config("llama-tiny", n_layers=4)
+        eng = NativeLlamaEngine(mc, ds, seq_len=32, device=torch.device("cpu"), seed=3)
+        step = eng.train_step
+        vocab = mc.vocab_size
+    else:
+        eng = initialize(_model(), ds, device="cpu")
+        vocab = VOCAB
+
+        def step(ids, lab):
+            eng.backward(eng(ids, lab))
+            return eng.step()
+    g = torch.Generator().manual_seed(100 + rank)
+    losses = []
+    for _ in range(3):
+        ids = torch.randint(0, vocab, (2, 32), generator=g)
+        losses.append(step(ids, ids)["loss"])
+    return losses, eng.param_offload, eng.shard_params.device.type, getattr(eng, "h2d_param_bytes", 0)
+
+
+@pytest.mark.parametrize("native", [True, False])
+@pytest.mark.parametrize("world", [1, 2])
+def test_offload_param_matches_resident_shards(native, world):
+    base = run_ranks(_poffload_rank, world, ("none", "none", native))
+    off = run_ranks(_poffload_rank, world, ("cpu", "cpu", native))
+    for (l0, on0, _, b0), (l1, on1, dev1, b1) in zip(base, off):
+        assert not on0 and b0 == 0
+        assert on1 and dev1 == "cpu" and b1 > 0          # every gather staged its rows from the host shard
+        assert l1 == l0
