@@ -241,6 +241,8 @@ class ClockSampler:
 # --------------------------------------------------------------------------- progress watchdog (multi-GPU runs)
 def beat(tag: str) -> None:
     """Progress mark for the supervising parent (no-op when not supervised)."""
+    if os.environ.get("B200ZERO_BENCH_TRACE") == "1":
+        print(f"[bench {time.strftime('%H:%M:%S')}] rank {os.environ.get('RANK', '0')}: {tag}", file=sys.stderr, flush=True)
     path = os.environ.get("B200ZERO_HEARTBEAT_FILE")
     if path:
         try:
@@ -706,6 +708,10 @@ def _fake_worker(args) -> int:
 
 def main() -> int:
     args = parse_args()
+    dump_after = float(os.environ.get("B200ZERO_BENCH_DUMP_AFTER", "0") or 0)
+    if dump_after > 0:                      # debugging aid: Python stacks of every thread if the run is still going then
+        import faulthandler
+        faulthandler.dump_traceback_later(dump_after, exit=False)
     if args.impl == "reference":
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
