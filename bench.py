@@ -59,6 +59,12 @@ def parse_args():
     ap.add_argument("--zero-stage", type=int, default=3)
     ap.add_argument("--engine", default="auto", help="auto | native | module (generic nn.Module ZeRO engine)")
     ap.add_argument("--attn", default=None, help="attention backend override: native | sdpa")
+    ap.add_argument("--offload-optimizer", default="none", choices=["none", "cpu", "nvme"],
+                    help="zero_optimization.offload_optimizer.device (BASELINE config 5: cpu)")
+    ap.add_argument("--offload-param", default="none", choices=["none", "cpu", "nvme"],
+                    help="zero_optimization.offload_param.device")
+    ap.add_argument("--grad-accum", type=int, default=1, help="gradient_accumulation_steps (micro-steps per timed step)")
+    ap.add_argument("--cpu-checkpointing", action="store_true", help="activation_checkpointing.cpu_checkpointing")
     ap.add_argument("--recompute", default=None, help="activation policy: none | light | selective | full | auto "
                     "(default: none for llama3-8b so that every N does the same work, auto otherwise)")
     ap.add_argument("--skip-e2e", action="store_true")
@@ -428,9 +434,10 @@ def run_ours(args) -> int:
     # The launcher's own auto-config drives the engine (public API path): ZeRO-3, bf16, no offload
     # (8B fits in 180 GB HBM3e per GPU even unsharded), clipping 1.0, WarmupDecayLR.
     ds_cfg = DeepSpeedConfig(model_name=args.model, zero_stage=ZeROStage(args.zero_stage),
-                             offload_optimizer=OffloadDevice.NONE, offload_param=OffloadDevice.NONE,
+                             offload_optimizer=OffloadDevice(args.offload_optimizer),
+                             offload_param=OffloadDevice(args.offload_param), cpu_checkpointing=args.cpu_checkpointing,
                              bf16_enabled=on_cuda, fp16_enabled=False, communication_data_type="bf16" if on_cuda else "fp32",
-                             train_micro_batch_size_per_gpu=MB, gradient_accumulation_steps=1,
+                             train_micro_batch_size_per_gpu=MB, gradient_accumulation_steps=args.grad_accum,
                              num_gpus=world, wall_clock_breakdown=False)
     ds_json = DeepSpeedLauncher().generate_config(ds_cfg)
     comm = args.comm
@@ -487,11 +494,23 @@ def run_ours(args) -> int:
         def elapsed_time(self, other):
             return (other.t - self.t) * 1e3
 
+    GAS = max(1, args.grad_accum)
+
+    def optimizer_step(i, from_host=False):
+        """One optimizer step = GAS micro-steps (forward + backward each), then clip + AdamW."""
+        m = None
+        for k in range(GAS):
+            a, b = (host if from_host else dev)[(i * GAS + k) % n_pool]
+            if from_host:
+                a, b = a.to(device, non_blocking=True), b.to(device, non_blocking=True)
+            m = engine.train_step(a, b)
+        return m
+
     # ---- warm-up ----
     beat("engine")
     loss_hist = []
     for i in range(args.warmup):
-        loss_hist.append(engine.train_step(*dev[i % n_pool])["loss"])
+        loss_hist.append(optimizer_step(i)["loss"])
         beat(f"warmup{i}")
     sync_all()
 
@@ -507,7 +526,7 @@ def run_ours(args) -> int:
     e0.record()
     last = None
     for i in range(args.steps):
-        last = engine.train_step(*dev[i % n_pool])
+        last = optimizer_step(i)
         loss_hist.append(last["loss"])               # already a host float (step() reads the stats vector)
     e1.record()
     sync_all()
@@ -520,7 +539,7 @@ def run_ours(args) -> int:
 
     # ---- end-to-end region: pinned H2D inputs + D2H loss read every step, wall clock ----
     e2e_ms = None
-    h2d = sum(t.numel() * t.element_size() for t in host[0])
+    h2d = GAS * sum(t.numel() * t.element_size() for t in host[0])
     # what the step reads back: ours — the 5-float stats vector (Σ‖g‖², flag, loss, ‖g‖, stop votes) read by
     # engine.step(); library arm — loss and gradient norm
     d2h = 8 if args.impl == "torch" else 4 * int(getattr(engine, "_stats_host", torch.zeros(5)).numel())
@@ -528,9 +547,7 @@ def run_ours(args) -> int:
         sync_all()
         t0 = time.perf_counter()
         for i in range(args.steps):
-            ids = host[i % n_pool][0].to(device, non_blocking=True)
-            lab = host[i % n_pool][1].to(device, non_blocking=True)
-            m = engine.train_step(ids, lab)
+            m = optimizer_step(i, from_host=True)
             loss_hist.append(float(m["loss"]))
             beat(f"e2e{i}")
         sync_all()
@@ -542,7 +559,7 @@ def run_ours(args) -> int:
         engine.cfg.wall_clock_breakdown = True
         sync_all()
         t0 = time.perf_counter()
-        m = engine.train_step(*dev[0])
+        m = optimizer_step(0)
         sync_all()
         breakdown = dict(m.get("timers_ms", {}), wall_ms=(time.perf_counter() - t0) * 1e3)
         engine.timers.enabled = False
@@ -552,7 +569,7 @@ def run_ours(args) -> int:
         from torch.profiler import ProfilerActivity, profile
         sync_all()
         with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-            engine.train_step(*dev[0])
+            optimizer_step(0)
             sync_all()
         if rank == 0:
             with open(args.torch_profile, "w") as f:
@@ -563,7 +580,7 @@ def run_ours(args) -> int:
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, e2e_total = float(t[0]), float(t[1])
-    tokens_per_step = MB * S * world
+    tokens_per_step = MB * S * world * GAS
     value = tokens_per_step * args.steps / (ms_total / 1e3)
     flops_tok = mcfg.flops_per_token(S, recompute=False)      # model FLOPs (6·N + attention): recompute not counted
     peaks = {}
@@ -579,7 +596,8 @@ def run_ours(args) -> int:
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if on_cuda else "fp32",
         "data": "synthetic tokens, random-init weights" + ("" if on_cuda else " [CPU SELF-TEST OF THE HARNESS: not a benchmark value]"),
         "config": {"model": args.model + (f"[TRUNCATED to {args.layers} layers: profiling only]" if args.layers else ""),
-                   "global_batch": MB * world, "seq_len": S,
+                   "global_batch": MB * world * GAS, "seq_len": S, "grad_accum": GAS,
+                   "offload_optimizer": args.offload_optimizer, "offload_param": args.offload_param,
                    "parallelism": f"zero{args.zero_stage}-dp{world}", "micro_batch_per_gpu": MB, "optimizer": "AdamW fp32 master",
                    "grad_clip": 1.0, "activation_recompute": engine.recompute, "comm": engine.comm_mode,
                    "attention": _attention_used(args),

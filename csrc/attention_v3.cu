@@ -75,9 +75,12 @@ flash_fwd_v3_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = S / F3_BM;
-  const int qi = nq - 1 - (int)(blockIdx.x % nq);  // heavy tiles first
-  const int h = (int)(blockIdx.x / nq) % Hq;
-  const int b = (int)(blockIdx.x / nq) / Hq;
+  // heavy tiles first over the whole grid (query tile qi visits qi + 1 KV blocks): every (head, batch) pair's last
+  // query tile is scheduled before anybody's second-to-last one; the 4 query heads of a KV group stay adjacent
+  const int groups = Hq * B;
+  const int qi = nq - 1 - (int)(blockIdx.x / groups);
+  const int h = (int)(blockIdx.x % groups) % Hq;
+  const int b = (int)(blockIdx.x % groups) / Hq;
   const int g = h / (Hq / Hk);
   const int row0 = b * S + qi * F3_BM;
   const int nblk = qi + 1;                         // causal: kv blocks 0..qi

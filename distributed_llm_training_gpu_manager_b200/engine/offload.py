@@ -16,6 +16,18 @@ from ..ops import lib as _lib
 _CHUNK = 1 << 26  # 64 Mi elements per chunk (128 MB bf16 down, 128 MB bf16 up)
 
 
+def host_threads(world_size: int) -> int:
+    """Worker threads for this rank's host optimizer: the cores this process may run on, shared fairly between the
+    ranks of the node (every rank runs its host AdamW at the same moment of the step)."""
+    import os
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        cores = os.cpu_count() or 1
+    local = int(os.environ.get("LOCAL_WORLD_SIZE", 0)) or max(1, world_size)
+    return max(1, int(os.environ.get("B200ZERO_HOST_ADAM_THREADS", 0)) or cores // local)
+
+
 def _host_lib():
     L = _lib.load_host(required=True)
     if not getattr(L, "_bz_bound", False):
@@ -59,6 +71,7 @@ def host_adam_step(engine, lr: float, step_no: int) -> None:
         engine._off_g = [torch.empty(min(CH, n), dtype=gdt).pin_memory() for _ in range(nbuf)]
         engine._off_p = [torch.empty(min(CH, n), dtype=torch.bfloat16).pin_memory() for _ in range(nbuf)]
     side = engine._off_stream
+    nthreads = host_threads(engine.world_size)
     side.wait_stream(torch.cuda.current_stream())
     chunks = [(o, min(o + CH, n)) for o in range(0, n, CH)]
     d2h_evt = [None] * len(chunks)
@@ -88,7 +101,7 @@ def host_adam_step(engine, lr: float, step_no: int) -> None:
             outp = engine._off_p[b][: hi - lo] if to_bf16 else None
         host_adamw(engine.master[lo:hi], engine.exp_avg[lo:hi], engine.exp_avg_sq[lo:hi], engine._off_g[b][: hi - lo],
                    outp, lr=lr, beta1=cfg.betas[0], beta2=cfg.betas[1], eps=cfg.eps, weight_decay=cfg.weight_decay,
-                   step=step_no, grad_scale=coef)
+                   step=step_no, grad_scale=coef, threads=nthreads)
         with torch.cuda.stream(side):
             if to_host_shard:
                 if not to_bf16:

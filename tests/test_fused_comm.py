@@ -320,3 +320,39 @@ def test_pull_allgather_v2_matches_v1_emulated():
     res = subprocess.run([sys.executable, "-c", _PULL_V2_CHECK % root], capture_output=True, text=True, timeout=150,
                          env=dict(os.environ))
     assert "PULL_V2_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
+
+
+def _fused_ckpt_rank(rank, world, tmp):
+    """Fused stage 3 with more resident blocks than the pipeline minimum: train, save, keep training (the weights
+    move on), load the checkpoint back and continue — the continuation must repeat the first one."""
+    import torch.distributed as dist
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.models import get_config
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
+    torch.cuda.set_device(rank)
+    mc = get_config("llama-tiny", n_layers=6)
+    ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=True, fp16_enabled=False,
+        train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
+        stage3_param_persistence_threshold=1000, stage3_max_live_parameters=4 * 600_000, wall_clock_breakdown=False))
+    eng = NativeLlamaEngine(mc, ds, seq_len=256, device=torch.device("cuda", rank), comm="fused", seed=5, recompute="none")
+    assert eng.comm_mode == "fused" and eng._n_pslots == 4, (eng.comm_mode, eng._n_pslots)
+    g = torch.Generator().manual_seed(300 + rank)
+    batches = [torch.randint(0, mc.vocab_size, (2, 256), generator=g).cuda() for _ in range(6)]
+    for b in batches[:3]:
+        eng.train_step(b, b)
+    eng.save_checkpoint(tmp)
+    first = [eng.train_step(b, b)["loss"] for b in batches[3:]]
+    eng.load_checkpoint(tmp)                       # peers' shards are restored and synchronised before any gather
+    assert eng.global_steps == 3
+    again = [eng.train_step(b, b)["loss"] for b in batches[3:]]
+    torch.cuda.synchronize(); dist.barrier(); eng.fused.close()
+    return first, again
+
+
+@pytest.mark.multigpu
+def test_fused_stage3_reload_with_wide_block_residency(tmp_path):
+    from dist_utils import run_ranks_nccl
+    world = min(torch.cuda.device_count(), 4)
+    for first, again in run_ranks_nccl(_fused_ckpt_rank, world, (str(tmp_path),), timeout=300):
+        assert again == pytest.approx(first, rel=2e-3)
