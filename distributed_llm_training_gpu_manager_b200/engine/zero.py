@@ -719,8 +719,9 @@ class ZeroEngine:
             return False
         from ..ops import lib as _oplib
         L = _oplib.load(required=True)
-        if hasattr(L, "bz_adamw_prefer_max_shared_carveout"):
-            L.bz_adamw_prefer_max_shared_carveout()
+        L.bz_adamw_prefer_max_shared_carveout()
+        # leave thread slots for one persistent GEMM CTA per SM (8 AdamW CTAs would occupy all 2048)
+        L.bz_adamw_set_ctas_per_sm(int(os.environ.get("B200ZERO_ADAM_OVERLAP_CTAS", "4")))
         self._adam_stream = torch.cuda.Stream(device=self.device)
         self._adam_coef = torch.ones(1, dtype=torch.float32, device=self.device)
         self._adam_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
