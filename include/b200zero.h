@@ -136,6 +136,25 @@ int bz_ipc_import(const unsigned char* handle64, void** out);
 int bz_ipc_close(void* p);
 int bz_enable_peer_access(int peer_device);
 
+/* ---- H2, second backend: CUDA virtual-memory management + NVSwitch multicast objects (csrc/vmm.cu) ----
+ * One exportable physical allocation per rank (cuMemCreate, POSIX file descriptor), mapped by every rank of the node;
+ * optionally bound into one multicast object whose mapping is what multimem.ld_reduce / multimem.st address.
+ * Set-up order, all ranks: bz_vmm_round_size -> bz_vmm_alloc -> exchange fds (unix sockets, parallel/symm.py) ->
+ * bz_vmm_import per peer. Multicast: rank 0 bz_mc_create, others bz_mc_import; everyone bz_mc_add_device; barrier;
+ * everyone bz_mc_bind_and_map. Driver entry points are resolved at run time (no libcuda link dependency).
+ * New scope: the reference has no communication layer. */
+int bz_vmm_supported(int* vmm, int* multicast);
+int bz_vmm_round_size(unsigned long long bytes, int world, unsigned long long* out);
+int bz_vmm_alloc(unsigned long long size, void** ptr, unsigned long long* handle, int* fd);
+int bz_vmm_import(int fd, unsigned long long size, void** ptr, unsigned long long* handle);
+int bz_vmm_unmap(void* ptr, unsigned long long size, unsigned long long handle);
+int bz_mc_create(int world, unsigned long long size, unsigned long long* mc_handle, int* fd);
+int bz_mc_import(int fd, unsigned long long* mc_handle);
+int bz_mc_add_device(unsigned long long mc_handle);
+int bz_mc_bind_and_map(unsigned long long mc_handle, unsigned long long mem_handle, unsigned long long size,
+                       void** mc_ptr);
+int bz_mc_unmap(void* mc_ptr, unsigned long long size, unsigned long long mc_handle);
+
 /* ---- K1: fused reduce-scatter + scale + accumulate + ‖g‖² + isfinite ---------------
  * Segment record (bz_comm_segment_bytes() = 32 bytes): {int64 full_off, int64 numel,
  * int64 shard_off, int32 partitioned, int32 pad}; element offsets, multiples of 16.

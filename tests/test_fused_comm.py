@@ -356,3 +356,34 @@ def test_fused_stage3_reload_with_wide_block_residency(tmp_path):
     world = min(torch.cuda.device_count(), 4)
     for first, again in run_ranks_nccl(_fused_ckpt_rank, world, (str(tmp_path),), timeout=300):
         assert again == pytest.approx(first, rel=2e-3)
+
+
+def _vmm_rank(rank, world):
+    """Own VMM allocator: every rank fills its buffer with its rank id; every rank then reads every peer's mapping."""
+    import torch.distributed as dist
+    from distributed_llm_training_gpu_manager_b200.parallel.symm import VmmSymmetricBuffer, _DevMem
+    torch.cuda.set_device(rank)
+    buf = VmmSymmetricBuffer(3 << 20, device=torch.device("cuda", rank))
+    assert buf.nbytes >= 3 << 20 and buf.nbytes % (2 << 20) == 0
+    mine = buf.tensor(torch.float32)
+    assert float(mine.abs().sum()) == 0.0                       # zero-filled
+    mine.fill_(float(rank + 1))
+    torch.cuda.synchronize(); dist.barrier()
+    seen = []
+    for r in range(world):
+        view = torch.as_tensor(_DevMem(buf.peer_ptrs[r], 4096), device=torch.device("cuda", rank)).view(torch.float32)
+        seen.append(float(view.clone()[7]))
+    torch.cuda.synchronize(); dist.barrier()
+    has_mc = bool(buf.multicast_ptr)
+    buf.close()
+    return seen, has_mc
+
+
+@pytest.mark.multigpu
+def test_vmm_symmetric_buffer_maps_every_peer():
+    from dist_utils import run_ranks_nccl
+    world = min(torch.cuda.device_count(), 4)
+    outs = run_ranks_nccl(_vmm_rank, world, timeout=240)
+    for seen, _ in outs:
+        assert seen == [float(r + 1) for r in range(world)]
+    assert len({mc for _, mc in outs}) == 1                     # all ranks agree on whether multicast was set up

@@ -183,3 +183,26 @@ def test_offload_param_matches_resident_shards(native, world):
         assert not on0 and b0 == 0
         assert on1 and dev1 == "cpu" and b1 > 0          # every gather staged its rows from the host shard
         assert l1 == l0
+
+
+# ---------------------------------------------------------------- descriptors travel between ranks (VMM handle exchange)
+def _fd_rank(rank, world):
+    import os
+    import tempfile
+    from distributed_llm_training_gpu_manager_b200.parallel.symm import exchange_fds
+    f = tempfile.TemporaryFile()
+    f.write(f"rank{rank}".encode()); f.flush()
+    got = exchange_fds([f.fileno()], rank, world, tag="t")
+    seen = []
+    for r in range(world):
+        fd = got[r][0]
+        seen.append(os.pread(fd, 16, 0).decode())
+        if r != rank:
+            os.close(fd)
+    return seen
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_file_descriptors_are_exchanged_all_to_all(world):
+    for seen in run_ranks(_fd_rank, world):
+        assert seen == [f"rank{r}" for r in range(world)]
