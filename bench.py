@@ -102,7 +102,11 @@ def measure_spike_to_halt(engine, batch, history, steps_needed=10):
     mon, policy = LossSpikeMonitor(), HaltPolicy()
     ids, lab = batch
     on_cuda = torch.cuda.is_available() and getattr(engine, "on_cuda", False)
-    while len(history) < steps_needed:              # the spike detector needs a 10-step window
+    # The spike detector compares a loss with the rolling window of the last 10: that window is filled with losses of
+    # the probe batch itself (10 ordinary steps), so "x50" means 50 times what the monitor has just been seeing — the
+    # benchmark's own loss history mixes four batches at different stages of being memorised and can hide it.
+    history = list(history)[:0]
+    while len(history) < steps_needed:
         engine.backward(engine(ids, lab))
         history.append(engine.step()["loss"])
     for i, loss in enumerate(history):

@@ -157,11 +157,9 @@ cast_bf16_to_f32_kernel(const __nv_bfloat16* __restrict__ in, float* __restrict_
     out[i] = __bfloat162float(in[i]);
 }
 
-static int g_adamw_ctas_per_sm = 8;      // bz_adamw_set_ctas_per_sm
-
-static inline int opt_grid(long long n, int per_thread, int ctas_per_sm = 8) {
+static inline int opt_grid(long long n, int per_thread) {
   long long blocks = (n / per_thread + OPT_THREADS - 1) / OPT_THREADS;
-  const long long cap = (long long)device_sm_count() * ctas_per_sm;
+  const long long cap = (long long)device_sm_count() * 8;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   return (int)blocks;
@@ -193,7 +191,7 @@ extern "C" int bz_adamw(float* master, float* m, float* v, const void* grad, int
              "adamw: buffers must be 16-byte aligned");
   const float bc1 = 1.f - powf(beta1, (float)step);
   const float bc2 = 1.f - powf(beta2, (float)step);
-  const int grid = opt_grid(n, 4, g_adamw_ctas_per_sm);
+  const int grid = opt_grid(n, 4);
   cudaStream_t st = (cudaStream_t)stream;
   if (grad_is_f32)
     adamw_kernel<true><<<grid, OPT_THREADS, 0, st>>>(master, m, v, grad, (__nv_bfloat16*)param_bf16, n, lr, beta1, beta2,
@@ -202,25 +200,6 @@ extern "C" int bz_adamw(float* master, float* m, float* v, const void* grad, int
     adamw_kernel<false><<<grid, OPT_THREADS, 0, st>>>(master, m, v, grad, (__nv_bfloat16*)param_bf16, n, lr, beta1, beta2,
                                                       eps, weight_decay, bc1, bc2, grad_scale, grad_scale_dev, skip_flag);
   BZ_CUDA_CHECK(cudaGetLastError());
-  return 0;
-}
-
-// The optimizer can be overlapped with the next forward pass (engine option): its CTAs then share SMs with
-// persistent GEMM CTAs that need ~200 KB of shared memory, so it must not pin the SM's L1/shared split to the
-// L1-heavy default (same reasoning as comm_kernels_setup_once in fused_comm.cu).
-extern "C" int bz_adamw_prefer_max_shared_carveout(void) {
-  BZ_CUDA_CHECK(cudaFuncSetAttribute(adamw_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                     cudaSharedmemCarveoutMaxShared));
-  BZ_CUDA_CHECK(cudaFuncSetAttribute(adamw_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                     cudaSharedmemCarveoutMaxShared));
-  return 0;
-}
-
-// How many AdamW CTAs (256 threads each, grid-stride) may sit on one SM. 8 (default) fills every thread slot, which is
-// right when the optimizer runs alone; an optimizer that overlaps the next forward pass leaves room for one GEMM CTA.
-extern "C" int bz_adamw_set_ctas_per_sm(int n) {
-  BZ_REQUIRE(n >= 1 && n <= 8, "adamw_set_ctas_per_sm: %d not in [1, 8]", n);
-  g_adamw_ctas_per_sm = n;
   return 0;
 }
 

@@ -185,7 +185,6 @@ class ZeroEngine:
         # in the per-step stats all-reduce, so every rank sees the same answer at the same step boundary.
         self.preempt_requested = False
         self._prefetch_evt: Dict[int, Any] = {}
-        self._adam_stream = None            # set by _enable_adam_overlap()
 
         # ---- parameters, units, layout ----
         self.source = module if isinstance(module, ParamSource) else None
@@ -655,8 +654,6 @@ class ZeroEngine:
             elif self._nvme is not None:
                 from .nvme import nvme_adam_step
                 nvme_adam_step(self, lr, step_no)
-            elif self._adam_stream is not None:
-                self._adam_overlapped(lr, step_no)
             elif self.state_device.type == "cpu" and self.on_cuda:
                 self._offloaded_adam(lr, step_no)
             else:
@@ -667,8 +664,11 @@ class ZeroEngine:
                              and not self.param_offload else None)
                 if not (self.compute_dtype == torch.bfloat16 and self.on_cuda) or self.param_offload:
                     self._refresh_shard_params()
-            if self.fused is None and self._adam_stream is None:
-                self.shard_grads.zero_()       # (the fused Adam kernel zeroes the shard as it reads it)
+            # the fused Adam kernel zeroes the shard as it reads it; a single-rank executor whose producers overwrite
+            # every gradient in place (gradients alias the shard) needs no zeroing at all
+            overwritten = self._grads_alias and not getattr(self, "_zero_after_reduce", True)
+            if self.fused is None and not overwritten:
+                self.shard_grads.zero_()
             # host read: the one sync of the step (feeds the loss monitor)
             if self.on_cuda:
                 self._stats_host.copy_(torch.stack([self._sumsq[0], self._flag[0].float(), st[2], self._norm[0] * inv_scale,
@@ -705,51 +705,6 @@ class ZeroEngine:
         self.last_metrics = m
         return m
 
-    # ------------------------------------------------------------------ optimizer / next-forward overlap (opt-in)
-    def _enable_adam_overlap(self) -> bool:
-        """Single-rank engines whose gradients alias the shard and are overwritten (never accumulated into) by their
-        producers: run AdamW unit by unit on a side stream and let the next forward wait per unit (the per-unit
-        events travel through ``_prefetch_evt``, which the executor already consumes before touching a unit).
-        AdamW is HBM-bound, the forward GEMMs are tensor-bound, so the two overlap; only the root unit's update
-        (embedding / head) stays exposed."""
-        ok = (self.on_cuda and self._single and self._grads_alias and self.source is not None and self.fused is None
-              and self._nvme is None and self.state_device.type == "cuda" and self.compute_dtype == torch.bfloat16
-              and not getattr(self, "_zero_after_reduce", True))
-        if not ok:
-            return False
-        from ..ops import lib as _oplib
-        L = _oplib.load(required=True)
-        L.bz_adamw_prefer_max_shared_carveout()
-        # leave thread slots for one persistent GEMM CTA per SM (8 AdamW CTAs would occupy all 2048)
-        L.bz_adamw_set_ctas_per_sm(int(os.environ.get("B200ZERO_ADAM_OVERLAP_CTAS", "4")))
-        self._adam_stream = torch.cuda.Stream(device=self.device)
-        self._adam_coef = torch.ones(1, dtype=torch.float32, device=self.device)
-        self._adam_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
-        return True
-
-    def _adam_overlapped(self, lr: float, step_no: int) -> None:
-        cfg, side = self.cfg, self._adam_stream
-        # the main stream recycles _coef / _flag for the next step while the side stream is still reading them
-        self._adam_coef.copy_(self._coef)
-        self._adam_flag.copy_(self._flag)
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            for u in self.layout.units:                      # forward order: root (embedding / head), then the blocks
-                a, b = u.repl_shard_start, u.repl_shard_end
-                if b > a:
-                    O.adamw_step(self.master[a:b], self.exp_avg[a:b], self.exp_avg_sq[a:b], self.shard_grads[a:b],
-                                 lr=lr, beta1=cfg.betas[0], beta2=cfg.betas[1], eps=cfg.eps,
-                                 weight_decay=cfg.weight_decay, step=step_no, grad_scale_dev=self._adam_coef,
-                                 skip_flag=self._adam_flag, param_out=self.shard_params[a:b])
-                evt = torch.cuda.Event()
-                evt.record(side)
-                self._prefetch_evt[u.index] = evt
-
-    def _join_adam(self) -> None:
-        """Anything that reads parameters or optimizer state outside the forward pass joins the side stream first."""
-        if self._adam_stream is not None:
-            torch.cuda.current_stream().wait_stream(self._adam_stream)
-
     def _offloaded_adam(self, lr: float, step_no: int) -> None:
         from .offload import host_adam_step
         host_adam_step(self, lr, step_no)
@@ -780,7 +735,6 @@ class ZeroEngine:
 
     def full_param(self, name: str) -> torch.Tensor:
         """Gathered fp32 master copy of one parameter (collective when partitioned)."""
-        self._join_adam()
         spec = self.layout.by_name[name]
         local = self.master[spec.shard_offset:spec.shard_offset + spec.shard_numel].to(self.device)
         if not spec.partitioned:
@@ -796,7 +750,6 @@ class ZeroEngine:
 
     def module_state_dict(self) -> Dict[str, torch.Tensor]:
         """16-bit (compute dtype) weights by name, gathered (``stage3_gather_16bit_weights_on_model_save``)."""
-        self._join_adam()
         sd = {}
         for u in self.layout.units:
             if not self._resident[u.index]:
@@ -809,7 +762,6 @@ class ZeroEngine:
         """Initialise the model from full (unsharded) tensors by parameter name — e.g. a converted Hugging Face
         checkpoint (``models/hf.py``) or the output of ``zero_to_fp32.py``. Every rank passes the same dict and keeps
         its own rows; Adam moments and step counters are left untouched. Returns the names that were not supplied."""
-        self._join_adam()
         missing = []
         for u in self.layout.units:
             for spec in u.params:
@@ -842,12 +794,10 @@ class ZeroEngine:
     def save_checkpoint(self, save_dir: str, tag: Optional[str] = None, client_state: Optional[Dict] = None,
                         async_write: bool = False):
         from .checkpoint import save_checkpoint
-        self._join_adam()
         return save_checkpoint(self, save_dir, tag, client_state or {}, async_write=async_write)
 
     def load_checkpoint(self, load_dir: str, tag: Optional[str] = None):
         from .checkpoint import load_checkpoint
-        self._join_adam()
         self._prefetch_evt.clear()
         return load_checkpoint(self, load_dir, tag)
 

@@ -212,9 +212,6 @@ class NativeLlamaEngine(ZeroEngine):
         # bulk gather / prefetch stream at all.
         self._ag_dgrad = (self._ag_fused and self.recompute in ("none", "light")
                           and os.environ.get("B200ZERO_AG_DGRAD", "0") == "1")
-        # AdamW of step t overlapped with the forward of step t+1 (single rank; opt-in until measured on hardware)
-        if os.environ.get("B200ZERO_ADAM_OVERLAP", "0") == "1":
-            self._enable_adam_overlap()
         self._act_offload = (ActivationOffloader(self.device)
                              if (self.cfg.cpu_checkpointing and self.on_cuda) else None)
 
@@ -375,10 +372,6 @@ class NativeLlamaEngine(ZeroEngine):
         T = B * S
         if self.pooled_params:
             self._ensure_resident(0)
-        elif self._adam_stream is not None:
-            evt = self._prefetch_evt.pop(0, None)
-            if evt is not None:
-                torch.cuda.current_stream().wait_event(evt)
         ids_flat, labels_flat = ids.reshape(-1), labels.reshape(-1)
         x = E.embedding_fwd(ids_flat, self.param_view("embed.weight"))
         for l in range(c.n_layers):
@@ -409,10 +402,6 @@ class NativeLlamaEngine(ZeroEngine):
         with self.timers.phase("forward"):
             if self.pooled_params:
                 self._ensure_resident(0)
-            elif self._adam_stream is not None:
-                evt = self._prefetch_evt.pop(0, None)          # root unit's AdamW (embedding / head) has finished
-                if evt is not None:
-                    torch.cuda.current_stream().wait_event(evt)
             ids_flat, labels_flat = ids.reshape(-1), labels.reshape(-1)
             x = E.embedding_fwd(ids_flat, self.param_view("embed.weight"))
             ckpts: List[torch.Tensor] = []

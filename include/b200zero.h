@@ -106,12 +106,6 @@ int bz_add_bf16(const void* a, const void* b, void* out, long long n, void* stre
 int bz_adamw(float* master, float* m, float* v, const void* grad, int grad_is_f32, void* param_bf16, long long n,
              float lr, float beta1, float beta2, float eps, float weight_decay, int step, float grad_scale,
              const float* grad_scale_dev, const int* skip_flag, void* stream);
-/* Ask for the max-shared-memory carveout for the AdamW kernel (needed when it runs concurrently with the
- * persistent GEMMs of the next forward pass: B200ZERO_ADAM_OVERLAP=1). */
-int bz_adamw_prefer_max_shared_carveout(void);
-/* CTAs of the AdamW kernel per SM (1..8, default 8 = every thread slot). An overlapped optimizer uses fewer so that
- * a persistent GEMM CTA fits next to them. */
-int bz_adamw_set_ctas_per_sm(int n);
 int bz_sumsq_workspace_floats(void);
 int bz_sumsq(const void* g, int g_is_f32, long long n, float* workspace, float* out, int accumulate,
              int* nonfinite_flag, void* stream);

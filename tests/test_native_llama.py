@@ -107,50 +107,6 @@ def test_capacity_planning_70b_on_8_b200():
     assert 120 * GB < s8["device_total"] < 140 * GB and s8["device_total"] + a8["light"] < 172 * GB
 
 
-_OVERLAP_CHECK = r"""
-import os, sys, torch
-sys.path.insert(0, %r)
-from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
-from distributed_llm_training_gpu_manager_b200.models import get_config
-from distributed_llm_training_gpu_manager_b200.models.native_llama import NativeLlamaEngine
-ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
-    zero_stage=3, offload_optimizer="none", offload_param="none", bf16_enabled=True, fp16_enabled=False,
-    train_micro_batch_size_per_gpu=2, gradient_accumulation_steps=1, learning_rate=1e-3, warmup_steps=1,
-    wall_clock_breakdown=False))
-mc = get_config("llama-tiny")
-res = {}
-for flag in ("0", "1"):
-    os.environ["B200ZERO_ADAM_OVERLAP"] = flag
-    eng = NativeLlamaEngine(mc, ds, seq_len=256, device=torch.device("cuda", 0), seed=3)
-    assert (eng._adam_stream is not None) == (flag == "1"), "overlap switch"
-    g = torch.Generator().manual_seed(0)
-    losses = []
-    for _ in range(6):
-        ids = torch.randint(0, mc.vocab_size, (2, 256), generator=g).cuda()
-        losses.append(eng.train_step(ids, ids)["loss"])
-    res[flag] = (losses, eng.full_param("blocks.1.w_down.weight").clone(), eng.full_param("lm_head.weight").clone())
-# the attention backward adds its dQ tiles in arrival order, so two serial runs already differ in the last bits
-# (measured: weights up to 3e-4 apart after 8 steps); the overlapped schedule must stay inside that noise
-for a, b in zip(res["0"][0], res["1"][0]):
-    assert abs(a - b) <= 1e-3 * abs(a), (res["0"][0], res["1"][0])
-assert res["0"][0][:2] == res["1"][0][:2]          # before any nondeterministic gradient has been applied twice
-assert torch.allclose(res["0"][1], res["1"][1], atol=2e-3) and torch.allclose(res["0"][2], res["1"][2], atol=2e-3)
-print("ADAM_OVERLAP_OK")
-"""
-
-
-@pytest.mark.gpu
-def test_adam_overlap_matches_serial_schedule():
-    """AdamW of step t on a side stream, unit by unit, while step t+1's forward runs: same arithmetic per element, so
-    losses and weights must agree with the serial schedule up to the run-to-run noise of the attention backward."""
-    import subprocess
-    import sys
-    from pathlib import Path
-    root = str(Path(__file__).resolve().parent.parent)
-    res = subprocess.run([sys.executable, "-c", _OVERLAP_CHECK % root], capture_output=True, text=True, timeout=150)
-    assert "ADAM_OVERLAP_OK" in res.stdout, res.stdout[-1500:] + res.stderr[-3000:]
-
-
 def test_eval_loss_matches_forward_and_leaves_state_alone():
     from distributed_llm_training_gpu_manager_b200.engine import initialize
     ds = DeepSpeedLauncher().generate_config(DeepSpeedConfig(
