@@ -17,8 +17,10 @@ TMO=420 run bench_torch   $TR --master-port 29602 bench.py --gpus $N --steps 20 
 B200ZERO_AG_DGRAD=1 TMO=300 run bench_ag_dgrad $TR --master-port 29603 bench.py --gpus $N --steps 8 --warmup 4 --skip-e2e --skip-halt --breakdown
 if [ "$MODE" = "full" ]; then
   B200ZERO_PULL_AG=2 TMO=300 run bench_pull_v2 $TR --master-port 29604 bench.py --gpus $N --steps 8 --warmup 4 --skip-e2e --skip-halt --breakdown
-  TMO=300 run bench_nccl $TR --master-port 29605 bench.py --gpus $N --steps 8 --warmup 4 --skip-e2e --skip-halt --impl nccl --breakdown
-  B200ZERO_PARAM_SLOTS=2 TMO=300 run bench_slots2 $TR --master-port 29606 bench.py --gpus $N --steps 8 --warmup 4 --skip-e2e --skip-halt --breakdown
+  if [ "${WITH_NCCL_ARM:-0}" = "1" ]; then
+    TMO=300 run bench_nccl $TR --master-port 29605 bench.py --gpus $N --steps 8 --warmup 4 --skip-e2e --skip-halt --impl nccl --breakdown
+    B200ZERO_PARAM_SLOTS=2 TMO=300 run bench_slots2 $TR --master-port 29606 bench.py --gpus $N --steps 8 --warmup 4 --skip-e2e --skip-halt --breakdown
+  fi
   B200ZERO_TEST_NVLS=1 TMO=300 run nvls_test python -m pytest tests/test_fused_comm.py -m gpu -q -k nvls
   B200ZERO_NVLS=1 TMO=300 run bench_nvls $TR --master-port 29607 bench.py --gpus $N --steps 8 --warmup 4 --skip-e2e --skip-halt --breakdown
   TMO=300 run bench_after_nvls $TR --master-port 29608 bench.py --gpus $N --steps 8 --warmup 4 --skip-e2e --skip-halt
