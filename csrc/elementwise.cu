@@ -2,6 +2,8 @@
 // All are 128-bit vectorised, keep fp32 statistics, and are launched with grids sized to
 // a multiple of the SM count. The reference has no kernels; these replace
 // the torch-eager ops a DeepSpeed user script would run (F3, F4, F5, F6, F11).
+#include <mutex>
+
 #include "common.cuh"
 #include "../include/b200zero.h"
 
@@ -592,11 +594,13 @@ static __device__ __align__(256) float g_rmsnorm_bwd_scratch[kStaticScratchFloat
 // Device address of g_rmsnorm_bwd_scratch per device ordinal. In host code the symbol name is only
 // a stand-in; the address a kernel may dereference has to come from cudaGetSymbolAddress.
 static float* g_scratch_addr[64] = {nullptr};
+static std::mutex g_scratch_mu;      // two host threads may make their first call on a device at the same time
 
 static int static_scratch_for_current_device(float** out) {
   int dev = -1;
   BZ_CUDA_CHECK(cudaGetDevice(&dev));
   BZ_REQUIRE(dev >= 0 && dev < 64, "rmsnorm_bwd_static_scratch: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
   if (g_scratch_addr[dev] == nullptr) {
     void* p = nullptr;
     BZ_CUDA_CHECK(cudaGetSymbolAddress(&p, g_rmsnorm_bwd_scratch));
