@@ -85,7 +85,7 @@ struct Segment {
   long long numel;      // full tensor size
   long long shard_off;  // element offset inside the rank's shard buffers
   int partitioned;      // 1: this rank owns rows [rank*numel/ws, (rank+1)*numel/ws); 0: replicated
-  int pad;
+  int push;             // K3 only: publish this tensor's updated rows even when the launch as a whole does not push
 };
 
 // -------------------------------------------------------------------------------------------------
@@ -407,7 +407,7 @@ fused_adam_push_kernel(const __grid_constant__ PeerTable pt, const Segment* __re
       w.x = pack_bf16x2(p[0], p[1]); w.y = pack_bf16x2(p[2], p[3]);
       w.z = pack_bf16x2(p[4], p[5]); w.w = pack_bf16x2(p[6], p[7]);
       if (shard_params != nullptr) *reinterpret_cast<uint4*>(shard_params + o) = w;
-      if (push) {
+      if (push || sg.push) {
         if (sg.partitioned) {
 #pragma unroll
           for (int q = 0; q < MAX_WS; ++q)   // own rows -> every rank's gathered parameter buffer

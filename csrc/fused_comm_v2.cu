@@ -27,7 +27,7 @@ struct C2Segment {      // must match Segment in fused_comm.cu (32 bytes)
   long long numel;
   long long shard_off;
   int partitioned;
-  int pad;
+  int push;
 };
 
 __device__ __forceinline__ uint4 c2_ld_peer(const void* p) {

@@ -320,7 +320,8 @@ class ZeroEngine:
             if cfg.max_reuse_distance < blk_numel:
                 self._n_pslots = 2               # nothing is worth keeping beyond the pipeline's own two buffers
             self._n_pslots = int(os.environ.get("B200ZERO_PARAM_SLOTS", self._n_pslots))
-            self._pbuf_root = torch.zeros(L.units[0].full_numel, dtype=cd, device=dev)
+            # symmetric (with the fused backend): the optimizer kernel publishes the root unit's new rows into it
+            self._pbuf_root = self._zeros(L.units[0].full_numel, cd, "pbuf_root", symmetric=True)
             self._pbuf_blk = [torch.zeros(blk_numel, dtype=cd, device=dev) for _ in range(self._n_pslots)]
             self._unit_pbuf = [self._pbuf_root] + [self._pbuf_blk[self._pslot(i)] for i in range(1, len(L.units))]
             self._resident = [False] * len(L.units)      # which unit's weights currently sit in its buffer
@@ -688,7 +689,10 @@ class ZeroEngine:
                 if self.stage >= 3 and self.pooled_params:
                     self._resident = [False] * len(L.units)
                     self._slot_owner = [None] * self._n_pslots
-                    self._gather_unit(0)
+                    if self.fused is not None and self.fused.can_push_root():
+                        self._resident[0] = True     # the optimizer kernel pushed the root unit's rows everywhere
+                    else:
+                        self._gather_unit(0)
                 elif self.fused is not None:
                     pass                        # rows were pushed into every rank's buffers by the Adam kernel
                 else:

@@ -36,9 +36,10 @@ def seg_len(spec, world_size: int) -> int:
 
 
 def segment_table(records: List[tuple], device) -> torch.Tensor:
-    """records: (full_off, numel, shard_off, partitioned) -> int64 [n, 4] device tensor whose rows
+    """records: (full_off, numel, shard_off, partitioned[, push]) -> int64 [n, 4] device tensor whose rows
     are the 32-byte Segment structs of csrc/fused_comm.cu."""
-    rows = [[fo, n, so, int(bool(part))] for fo, n, so, part in records]   # int32 partitioned + int32 pad = 1 int64 (LE)
+    # int32 partitioned + int32 push = one little-endian int64
+    rows = [[r[0], r[1], r[2], int(bool(r[3])) | ((int(bool(r[4])) << 32) if len(r) > 4 else 0)] for r in records]
     assert all(r[1] % 8 == 0 for r in rows), "fused kernels walk whole 8-element vectors"
     return torch.tensor(rows, dtype=torch.int64, device=device).contiguous()
 
@@ -46,6 +47,7 @@ def segment_table(records: List[tuple], device) -> torch.Tensor:
 class FusedComm:
     def __init__(self, engine, rs_ctas: Optional[int] = None, adam_ctas: Optional[int] = None):
         import os
+        self.push_root = False
         rs_ctas = rs_ctas or int(os.environ.get("B200ZERO_RS_CTAS", "128"))
         adam_ctas = adam_ctas or int(os.environ.get("B200ZERO_ADAM_CTAS", "148"))
         self.nvls_ctas = int(os.environ.get("B200ZERO_NVLS_CTAS", "32"))
@@ -176,10 +178,17 @@ class FusedComm:
             segs, nseg, pptrs = self._all_segs, self._all_segs.shape[0], self._all_ptrs
         else:
             if not hasattr(self, "_all_segs"):
-                recs = [(0, seg_len(s, e.world_size), s.shard_offset, s.partitioned)
+                # Stage 3: blocks are re-gathered when they run, but the root unit (embedding, final norm, LM head)
+                # is needed by every step from its first kernel on. Its updated rows are published here, by the
+                # optimizer kernel itself, into every rank's gathered root buffer (per-segment push flag) — there
+                # is no separate gather of the root unit after the step.
+                self.push_root = self.can_push_root()
+                recs = [(s.full_offset if (self.push_root and u.index == 0) else 0, seg_len(s, e.world_size),
+                         s.shard_offset, s.partitioned, self.push_root and u.index == 0)
                         for u in e.layout.units for s in u.params]
                 self._all_segs = segment_table(recs, e.device)
-            segs, nseg, pptrs = self._all_segs, self._all_segs.shape[0], None
+                self._root_ptrs = self._ptrs_for(e._pbuf_root) if self.push_root else None
+            segs, nseg, pptrs = self._all_segs, self._all_segs.shape[0], self._root_ptrs
         tail = (segs.data_ptr(), nseg, e.master.data_ptr(), e.exp_avg.data_ptr(),
                 e.exp_avg_sq.data_ptr(), e.shard_grads.data_ptr(), int(e.shard_grads.dtype == torch.float32),
                 e.shard_params.data_ptr(), lr, cfg.betas[0], cfg.betas[1], cfg.eps, cfg.weight_decay, step_no,
@@ -187,6 +196,12 @@ class FusedComm:
                 ADAM_CHANNEL, e.rank, e.world_size, push, 1, 1, self.adam_ctas, _lib.stream())
         rc = self.L.bz_fused_adam_push(pptrs, self._sig_ptrs, *tail)
         _lib.check(rc, "fused_adam_push")
+
+    def can_push_root(self) -> bool:
+        import os
+        e = self.e
+        return bool(e.stage >= 3 and e.pooled_params and "pbuf_root" in e._symm
+                    and os.environ.get("B200ZERO_PUSH_ROOT", "1") == "1")
 
     def close(self) -> None:
         self.signal.close()

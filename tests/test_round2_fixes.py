@@ -206,3 +206,12 @@ def _fd_rank(rank, world):
 def test_file_descriptors_are_exchanged_all_to_all(world):
     for seen in run_ranks(_fd_rank, world):
         assert seen == [f"rank{r}" for r in range(world)]
+
+
+def test_segment_table_packs_partitioned_and_push_into_one_word():
+    from distributed_llm_training_gpu_manager_b200.parallel.fused import segment_table
+    t = segment_table([(0, 64, 0, True), (64, 16, 128, False, True), (80, 32, 256, True, True)], "cpu")
+    assert t.shape == (3, 4) and t.dtype == torch.int64
+    flags = t[:, 3].tolist()
+    assert [f & 0xFFFFFFFF for f in flags] == [1, 0, 1]          # int32 partitioned (low half, little endian)
+    assert [f >> 32 for f in flags] == [0, 1, 1]                  # int32 push (high half)
