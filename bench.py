@@ -249,8 +249,12 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- progress watchdog (multi-GPU runs)
+_LAST_BEAT = [time.time(), "start"]
+
+
 def beat(tag: str) -> None:
     """Progress mark for the supervising parent (no-op when not supervised)."""
+    _LAST_BEAT[0], _LAST_BEAT[1] = time.time(), tag
     if os.environ.get("B200ZERO_BENCH_TRACE") == "1":
         print(f"[bench {time.strftime('%H:%M:%S')}] rank {os.environ.get('RANK', '0')}: {tag}", file=sys.stderr, flush=True)
     path = os.environ.get("B200ZERO_HEARTBEAT_FILE")
@@ -509,6 +513,29 @@ def run_ours(args) -> int:
                 a, b = a.to(device, non_blocking=True), b.to(device, non_blocking=True)
             m = engine.train_step(a, b)
         return m
+
+    # ---- stall watchdog (debugging aid, B200ZERO_BENCH_WATCHDOG_S=<seconds>): if no progress mark appears for that
+    #      long, print every thread's Python stack and the fused backend's view of the cross-GPU flags, once ----
+    wd_s = float(os.environ.get("B200ZERO_BENCH_WATCHDOG_S", "0") or 0)
+    if wd_s > 0:
+        import faulthandler
+
+        def _watch():
+            fired = False
+            while not fired:
+                time.sleep(1.0)
+                if time.time() - _LAST_BEAT[0] > wd_s:
+                    fired = True
+                    print(f"[bench watchdog] rank {rank}: no progress for {wd_s:.0f} s after mark '{_LAST_BEAT[1]}'",
+                          file=sys.stderr, flush=True)
+                    faulthandler.dump_traceback(file=sys.stderr, all_threads=True)
+                    try:
+                        fused = getattr(engine, "fused", None)
+                        if fused is not None:
+                            print(f"[bench watchdog] {json.dumps(fused.debug_snapshot())}", file=sys.stderr, flush=True)
+                    except Exception as exc:  # noqa: BLE001
+                        print(f"[bench watchdog] snapshot failed: {exc}", file=sys.stderr, flush=True)
+        threading.Thread(target=_watch, daemon=True).start()
 
     # ---- warm-up ----
     beat("engine")

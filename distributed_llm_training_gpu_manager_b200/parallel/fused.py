@@ -134,6 +134,7 @@ class FusedComm:
             rc = self.L.bz_fused_reduce_scatter(self._ptrs_for(gb), self._sig_ptrs, *tail)
         _lib.check(rc, "fused_reduce_scatter")
         _lib.add_launches(1)
+        self.launches += 1
         return True
 
     # -- control exchange ------------------------------------------------------------------------
@@ -196,6 +197,26 @@ class FusedComm:
                 ADAM_CHANNEL, e.rank, e.world_size, push, 1, 1, self.adam_ctas, _lib.stream())
         rc = self.L.bz_fused_adam_push(pptrs, self._sig_ptrs, *tail)
         _lib.check(rc, "fused_adam_push")
+
+    def debug_snapshot(self) -> dict:
+        """What this rank's signal pad and host-side epoch counters look like right now, read on a private stream
+        (works while the main / communication streams are stuck behind a kernel that waits for a peer). For every
+        channel and phase: the epoch each rank has announced to us. Used by bench.py's stall watchdog."""
+        side = torch.cuda.Stream(device=self.e.device)
+        words = self.L.bz_comm_signal_pad_bytes() // 4
+        host = torch.zeros(words, dtype=torch.int32).pin_memory()
+        with torch.cuda.stream(side):
+            host.copy_(self.signal.tensor(torch.int32, words), non_blocking=True)
+        side.synchronize()
+        ws, tab = self.e.world_size, host.tolist()
+        names = {RS_CHANNEL: "reduce_scatter", ADAM_CHANNEL: "adam", STATS_CHANNEL: "stats"}
+        pad = {}
+        for ch, nm in names.items():
+            for ph in range(3):
+                base = (ch * 3 + ph) * int(self.L.bz_comm_max_world())
+                pad[f"{nm}.phase{ph}"] = [v & 0xFFFFFFFF for v in tab[base:base + ws]]
+        return {"rank": self.e.rank, "host_epochs": {names[k]: v for k, v in self.epoch.items()}, "announced_to_me": pad,
+                "k1_launches": self.launches}
 
     def can_push_root(self) -> bool:
         import os
