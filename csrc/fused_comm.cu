@@ -635,7 +635,9 @@ int bz_fused_adam_push(void* const* param_ptrs, void* const* signal_ptrs, const 
                        void* stream) {
   PeerTable pt;
   void* nulls[MAX_WS] = {nullptr};
-  if (int rc = fill_table(pt, push ? param_ptrs : nulls, signal_ptrs, ws)) return rc;
+  // the table is also needed when only some segments publish their rows (Segment::push) in a launch with push == 0
+  BZ_REQUIRE(!push || param_ptrs != nullptr, "fused_adam_push: push requested without parameter buffers");
+  if (int rc = fill_table(pt, param_ptrs != nullptr ? param_ptrs : nulls, signal_ptrs, ws)) return rc;
   BZ_REQUIRE(step >= 1, "fused_adam_push: step must be >= 1");
   BZ_REQUIRE(channel >= 0 && channel < SIG_CHANNELS, "fused_adam_push: channel %d out of range", channel);
   if (ctas <= 0) ctas = 128;

@@ -387,3 +387,44 @@ def test_vmm_symmetric_buffer_maps_every_peer():
     for seen, _ in outs:
         assert seen == [float(r + 1) for r in range(world)]
     assert len({mc for _, mc in outs}) == 1                     # all ranks agree on whether multicast was set up
+
+
+def test_adam_publishes_only_flagged_segments_emulated():
+    """Stage-3 flavour of K3: the launch as a whole does not push (push = 0), but segments that carry the push flag
+    (the root unit's tensors) still land in every rank's gathered buffer; the others only update the local shard."""
+    L = bz.load(required=True)
+    recs, unit_numel, shard_numel = _layout()
+    # publish the first partitioned tensor and the replicated one; keep the rest local
+    part_idx = [i for i, r in enumerate(recs) if r[3]]
+    flagged = {part_idx[0]} | {i for i, r in enumerate(recs) if not r[3]}
+    segs = segment_table([r + (i in flagged,) for i, r in enumerate(recs)], "cuda")
+    torch.manual_seed(2)
+    full0 = torch.randn(unit_numel, device="cuda")
+    gfull = torch.randn(unit_numel, device="cuda")
+    ref_p = torch.nn.Parameter(full0.clone())
+    ref_p.grad = gfull.clone()
+    torch.optim.AdamW([ref_p], lr=1e-2, weight_decay=0.01).step()
+    params = [torch.zeros(unit_numel, device="cuda", dtype=torch.bfloat16) for _ in range(W)]
+    ws = torch.zeros(L.bz_fused_comm_workspace_bytes() // 4, device="cuda")
+    coef = torch.ones(1, device="cuda")
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for r in range(W):
+        master = torch.zeros(shard_numel, device="cuda"); g = torch.zeros(shard_numel, device="cuda")
+        for fo, n, so, part in recs:
+            sl = slice(fo + r * (n // W), fo + (r + 1) * (n // W)) if part else slice(fo, fo + n)
+            cnt = n // W if part else n
+            master[so:so + cnt] = full0[sl]; g[so:so + cnt] = gfull[sl]
+        m, v = torch.zeros_like(master), torch.zeros_like(master)
+        sp = torch.zeros(shard_numel, device="cuda", dtype=torch.bfloat16)
+        rc = L.bz_fused_adam_push(_ptrs(params), None, segs.data_ptr(), len(recs), master.data_ptr(), m.data_ptr(),
+                                  v.data_ptr(), g.data_ptr(), 1, sp.data_ptr(), 1e-2, 0.9, 0.999, 1e-8, 0.01, 1,
+                                  coef.data_ptr(), flag.data_ptr(), ws.data_ptr(), 1, 1, r, W, 0, 0, 1, 16, bz.stream())
+        bz.check(rc, "adam_push")
+        torch.cuda.synchronize()
+    for q in range(W):
+        for i, (fo, n, so, part) in enumerate(recs):
+            got = params[q][fo:fo + n].float()
+            if i in flagged and part:
+                assert torch.allclose(got, ref_p.data[fo:fo + n], rtol=1e-2, atol=1e-2), (q, i)
+            elif i not in flagged:
+                assert float(got.abs().sum()) == 0.0, (q, i)       # never published
