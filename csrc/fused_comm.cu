@@ -58,58 +58,6 @@ __device__ __forceinline__ void st_peer_v4(void* p, uint4 v) {
                : "memory");
 }
 
-// A wait for a peer's flag is bounded: after g_comm_timeout_ns the waiting thread records what it was waiting for
-// (first record wins) and gives up, so a lost peer turns into an error the host reads at its next synchronisation
-// point (bz_comm_get_error) instead of a kernel that spins forever. The data the kernel goes on to produce is
-// meaningless after that; the engine raises before using it.
-struct CommError {
-  int code;              // 0 = none, 1 = timed out waiting for a peer's flag
-  int channel, phase;
-  int waiting_for;       // rank whose announcement did not arrive
-  unsigned int epoch;    // value waited for
-  unsigned int seen;     // last value read
-  int rank;              // this rank
-  int cta;
-};
-__device__ CommError g_comm_error;
-__device__ unsigned long long g_comm_timeout_ns = 30ull * 1000000000ull;
-
-__device__ __forceinline__ unsigned long long comm_now_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-__device__ __noinline__ void comm_report_timeout(int channel, int phase, int src, uint32_t epoch, uint32_t seen, int rank) {
-  if (atomicCAS(&g_comm_error.code, 0, 1) == 0) {
-    g_comm_error.channel = channel;
-    g_comm_error.phase = phase;
-    g_comm_error.waiting_for = src;
-    g_comm_error.epoch = epoch;
-    g_comm_error.seen = seen;
-    g_comm_error.rank = rank;
-    g_comm_error.cta = (int)blockIdx.x;
-    __threadfence_system();
-  }
-}
-
-// Out of line on purpose: the timer bookkeeping must not add to the register footprint of the kernels that call it
-// (they are sized to share an SM with a persistent GEMM CTA).
-__device__ __noinline__ void comm_wait_flag(const uint32_t* f, uint32_t epoch, int channel, int phase, int src, int rank) {
-  unsigned ns = 32;
-  const unsigned long long t0 = comm_now_ns();
-  const unsigned long long limit = g_comm_timeout_ns;
-  // epochs only grow; signed distance handles wrap-around
-  uint32_t seen;
-  while ((int32_t)((seen = ld_acquire_sys(f)) - epoch) < 0) {
-    __nanosleep(ns);
-    if (ns < 1024) ns <<= 1;
-    if (comm_now_ns() - t0 > limit) {
-      comm_report_timeout(channel, phase, src, epoch, seen, rank);
-      break;
-    }
-  }
-}
-
 // Announce `epoch` on (channel, phase) to every rank, then wait until every rank announced it.
 // Called by all threads of a CTA; only CTA 0 announces. Safe against reordering of this CTA's
 // earlier global writes (fence) and later reads (acquire + barrier).
@@ -121,7 +69,13 @@ __device__ __forceinline__ void signal_all_and_wait(const PeerTable& pt, int cha
     st_release_sys(pt.signal[threadIdx.x] + sig_index(channel, phase, rank), epoch);
   }
   if (threadIdx.x < ws) {
-    comm_wait_flag(pt.signal[rank] + sig_index(channel, phase, threadIdx.x), epoch, channel, phase, (int)threadIdx.x, rank);
+    const uint32_t* f = pt.signal[rank] + sig_index(channel, phase, threadIdx.x);
+    unsigned ns = 32;
+    // epochs only grow; signed distance handles wrap-around
+    while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+      __nanosleep(ns);
+      if (ns < 1024) ns <<= 1;
+    }
   }
   __syncthreads();
 }
@@ -568,26 +522,6 @@ using namespace bz;
 extern "C" {
 
 int bz_comm_max_world(void) { return MAX_WS; }
-
-// How long a kernel waits for a peer's flag before it records an error and gives up (default 30 s).
-int bz_comm_set_timeout_ms(unsigned int ms) {
-  const unsigned long long ns = (unsigned long long)ms * 1000000ull;
-  BZ_CUDA_CHECK(cudaMemcpyToSymbol(g_comm_timeout_ns, &ns, sizeof(ns)));
-  return 0;
-}
-// out8: {code, channel, phase, waiting_for_rank, epoch, seen, rank, cta}; code 0 = no error. With clear != 0 the
-// record is reset afterwards. Synchronous 32-byte copy: call it where the host synchronises anyway.
-int bz_comm_get_error(int* out8, int clear) {
-  CommError e;
-  BZ_CUDA_CHECK(cudaMemcpyFromSymbol(&e, g_comm_error, sizeof(e)));
-  out8[0] = e.code; out8[1] = e.channel; out8[2] = e.phase; out8[3] = e.waiting_for;
-  out8[4] = (int)e.epoch; out8[5] = (int)e.seen; out8[6] = e.rank; out8[7] = e.cta;
-  if (clear && e.code != 0) {
-    CommError z = {};
-    BZ_CUDA_CHECK(cudaMemcpyToSymbol(g_comm_error, &z, sizeof(z)));
-  }
-  return 0;
-}
 int bz_comm_signal_pad_bytes(void) { return (SIG_CHANNELS * SIG_PHASES * MAX_WS + 64) * (int)sizeof(uint32_t); }
 int bz_comm_segment_bytes(void) { return (int)sizeof(Segment); }
 int bz_comm_max_ctas(void) { return 1024; }

@@ -676,8 +676,6 @@ class ZeroEngine:
                                                     stop_votes]), non_blocking=True)
                 torch.cuda.current_stream().synchronize()
                 vals = self._stats_host.tolist()
-                if self.fused is not None:
-                    self.fused.check_health()      # a kernel that gave up waiting for a peer: raise, do not train on
             else:
                 vals = [float(self._sumsq[0]), float(self._flag[0]), float(st[2]), float(self._norm[0]) * inv_scale,
                         float(stop_votes)]

@@ -14,8 +14,6 @@ Division of labour per optimizer step (cf. ``engine/zero.py`` which does the sam
 """
 from __future__ import annotations
 
-import ctypes as C
-import os
 from typing import Dict, List, Optional
 
 import torch
@@ -79,9 +77,6 @@ class FusedComm:
                 [(s.full_offset, seg_len(s, engine.world_size), s.shard_offset, s.partitioned) for s in u.params], dev)
         self.launches = 0
         self.nvls_launches = 0
-        tmo = os.environ.get("B200ZERO_COMM_TIMEOUT_MS")
-        if tmo:
-            _lib.check(self.L.bz_comm_set_timeout_ms(C.c_uint(int(tmo))), "comm_set_timeout_ms")
 
     # -- symmetric buffers are created by the engine through this hook --------------------------------
     @staticmethod
@@ -202,18 +197,6 @@ class FusedComm:
                 ADAM_CHANNEL, e.rank, e.world_size, push, 1, 1, self.adam_ctas, _lib.stream())
         rc = self.L.bz_fused_adam_push(pptrs, self._sig_ptrs, *tail)
         _lib.check(rc, "fused_adam_push")
-
-    def check_health(self) -> None:
-        """Raise if a fused kernel gave up waiting for a peer since the last call (called by the engine right after
-        the step's host synchronisation; a 32-byte device read)."""
-        out = (C.c_int * 8)()
-        _lib.check(self.L.bz_comm_get_error(out, 1), "comm_get_error")
-        if out[0] != 0:
-            names = {RS_CHANNEL: "reduce-scatter", ADAM_CHANNEL: "adam/publish", STATS_CHANNEL: "control exchange"}
-            raise RuntimeError(
-                f"fused collective timed out on rank {out[6]}: {names.get(out[1], out[1])} phase {out[2]} waited for "
-                f"rank {out[3]} to announce epoch {out[4] & 0xFFFFFFFF} but last saw {out[5] & 0xFFFFFFFF} (CTA {out[7]}). "
-                f"A peer is lost or stalled; results of this step are invalid.")
 
     def debug_snapshot(self) -> dict:
         """What this rank's signal pad and host-side epoch counters look like right now, read on a private stream

@@ -120,11 +120,6 @@ int bz_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream);
  * (torch.distributed all_gather in parallel/symm.py). New scope: the reference has no
  * communication backend at all. */
 int bz_comm_max_world(void);
-/* Waits for a peer's flag inside K1 / K3 / the control exchange are bounded (default 30 s): on expiry the kernel
- * records {code, channel, phase, waiting_for_rank, epoch, seen, rank, cta} and stops waiting; the host reads the
- * record where it synchronises anyway (the engine does, once per optimizer step) and raises. */
-int bz_comm_set_timeout_ms(unsigned int ms);
-int bz_comm_get_error(int* out8, int clear);
 int bz_comm_signal_pad_bytes(void);
 int bz_comm_segment_bytes(void);
 int bz_fused_comm_workspace_bytes(void);
