@@ -99,7 +99,9 @@ fused_reduce_scatter_kernel(const __grid_constant__ PeerTable pt, const Segment*
                             uint32_t epoch, int channel, int rank, int ws, int use_barrier) {
   __shared__ float red[32];
   __shared__ int is_last;
-  if (use_barrier) signal_all_and_wait(pt, channel, 0, rank, ws, epoch, blockIdx.x == 0);
+  // use_barrier: 1 = phase 0 in this kernel (every CTA waits until all ranks' buffers are ready) + phase 1;
+  //              2 = phase 0 was done by comm_ready_kernel in front of this launch, only phase 1 here
+  if (use_barrier == 1) signal_all_and_wait(pt, channel, 0, rank, ws, epoch, blockIdx.x == 0);
 
   float ss_part = 0.f, ss_repl = 0.f;
   for (int s = 0; s < nseg; ++s) {
@@ -178,6 +180,16 @@ fused_reduce_scatter_kernel(const __grid_constant__ PeerTable pt, const Segment*
       signal_all_and_wait(pt, channel, 1, rank, ws, epoch, true);
     }
   }
+}
+
+// Phase 0 of K1 as a launch of its own: one warp announces "my buffer for this epoch is complete" to every rank and
+// waits until every rank has said the same; the reduce kernel behind it on the stream then starts with all inputs
+// ready and none of its CTAs ever spins for a peer. Done inside the reduce kernel (use_barrier == 1), all of its
+// CTAs sit on their SMs polling until the slowest rank arrives — registers and thread slots the compute kernels of
+// the backward pass could be using, and at 8 ranks long runs stalled that way.
+__global__ void __launch_bounds__(32)
+comm_ready_kernel(const __grid_constant__ PeerTable pt, int channel, int rank, int ws, uint32_t epoch) {
+  signal_all_and_wait(pt, channel, 0, rank, ws, epoch, true);
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -502,6 +514,7 @@ static void comm_kernels_setup_once() {
   prefer_max_shared_carveout(fused_adam_push_kernel<false>);
   prefer_max_shared_carveout(pull_allgather_kernel);
   prefer_max_shared_carveout(fold_partials_kernel);
+  prefer_max_shared_carveout(comm_ready_kernel);
   done = true;
 }
 
@@ -580,6 +593,11 @@ int bz_fused_reduce_scatter(void* const* grad_ptrs, void* const* signal_ptrs, co
   if (ctas > 1024) ctas = 1024;
   cudaStream_t st = (cudaStream_t)stream;
   unsigned int* counter = reinterpret_cast<unsigned int*>(workspace + 2 * 1024);
+  if (use_barrier == 3) {          // phase 0 in front of the reduce kernel instead of inside every one of its CTAs
+    comm_ready_kernel<<<1, 32, 0, st>>>(pt, channel, rank, ws, epoch);
+    BZ_CUDA_CHECK(cudaGetLastError());
+    use_barrier = 2;
+  }
   if (shard_is_f32)
     fused_reduce_scatter_kernel<true><<<ctas, COMM_THREADS, 0, st>>>(pt, (const Segment*)segs, nseg, shard_grads, scale,
                                                                      workspace, workspace + ctas, nonfinite_flag, counter,

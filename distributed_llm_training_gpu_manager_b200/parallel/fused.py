@@ -54,6 +54,9 @@ class FusedComm:
         self.pull_version = int(os.environ.get("B200ZERO_PULL_AG", "1"))   # 2: division-free kernel (fused_comm_v2.cu)
         self.use_fused_gather = os.environ.get("B200ZERO_FUSED_GATHER", "1") == "1"
         self.use_fused_rs = os.environ.get("B200ZERO_FUSED_RS", "1") == "1"
+        # 3: the "all ranks ready" wait of K1 is a one-warp launch in front of the reduce kernel (default);
+        # 1: every CTA of the reduce kernel waits itself (B200ZERO_RS_SPLIT_WAIT=0)
+        self.rs_barrier = 3 if os.environ.get("B200ZERO_RS_SPLIT_WAIT", "1") == "1" else 1
         assert engine.on_cuda, "fused communication needs GPUs"
         self.e = engine
         self.L = _lib.load(required=True)
@@ -124,7 +127,7 @@ class FusedComm:
         tail = (self._unit_segs[ui].data_ptr(), len(e.layout.units[ui].params),
                 e.shard_grads.data_ptr(), int(e.shard_grads.dtype == torch.float32), scale, self.workspace.data_ptr(),
                 self.sumsq_part.data_ptr(), self.sumsq_repl.data_ptr(), e._flag.data_ptr(), self.epoch[RS_CHANNEL],
-                RS_CHANNEL, e.rank, e.world_size, 1, self.rs_ctas, _lib.stream())
+                RS_CHANNEL, e.rank, e.world_size, self.rs_barrier, self.rs_ctas, _lib.stream())
         mc = self._mc_for(gb)
         if mc:
             tail = tail[:-2] + (self.nvls_ctas, tail[-1])      # the switch does the summing: fewer CTAs suffice

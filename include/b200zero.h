@@ -152,6 +152,8 @@ int bz_mc_unmap(void* mc_ptr, unsigned long long size, unsigned long long mc_han
 /* ---- K1: fused reduce-scatter + scale + accumulate + ‖g‖² + isfinite ---------------
  * Segment record (bz_comm_segment_bytes() = 32 bytes): {int64 full_off, int64 numel,
  * int64 shard_off, int32 partitioned, int32 pad}; element offsets, multiples of 16.
+ * use_barrier: 0 = none (single process / emulated ranks), 1 = every CTA waits for all ranks' buffers (phase 0) and the
+ * last CTA for all ranks' reads (phase 1), 3 = phase 0 runs as a one-warp launch in front of the reduce kernel.
  * grad_ptrs[ws] / signal_ptrs[ws]: peer-mapped pointers, index = rank. workspace:
  * bz_fused_comm_workspace_bytes() bytes, zeroed once. epoch must increase by one per
  * call per channel on every rank. use_barrier=0 skips the cross-rank flags (single-GPU
