@@ -18,9 +18,10 @@ Llama-3-8B, which fits at every N) instead of being chosen from free memory.
 
 Multi-GPU runs (WORLD_SIZE > 1) execute in one supervised child process per rank (``supervise``): the
 child does all the work and prints the line; the parent watches a heartbeat file. If the default run
-stops making progress (the fused collectives wait on peer flags inside kernels) or dies, it is re-run
-once with ``--comm nccl`` and the line says so three times over: ``"fallback"``, ``"impl": "ours-nccl-fallback"``
-and ``"comm": "nccl"`` in its config. Both attempts together stay inside ``B200ZERO_BENCH_BUDGET_S`` (800 s).
+stops making progress (the fused collectives wait on peer flags inside kernels) or dies, it is tried once more as it
+is (the line then carries ``"retried"``) and, failing that, re-run with ``--comm nccl``; that line says so three times
+over: ``"fallback"``, ``"impl": "ours-nccl-fallback"`` and ``"comm": "nccl"`` in its config. All attempts together
+stay inside ``B200ZERO_BENCH_BUDGET_S`` (800 s).
 ``B200ZERO_BENCH_SUPERVISE=0`` runs in-process as for N = 1.
 
 ``--impl reference`` runs the unmodified reference from ``baseline/_ref`` through its own public
@@ -74,6 +75,7 @@ def parse_args():
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model (result is not a bench value)")
     ap.add_argument("--worker", action="store_true", help=argparse.SUPPRESS)         # set by supervise()
     ap.add_argument("--fallback-note", default=None, help=argparse.SUPPRESS)         # set by supervise()
+    ap.add_argument("--retry-note", default=None, help=argparse.SUPPRESS)            # set by supervise()
     return ap.parse_args()
 
 
@@ -296,10 +298,14 @@ def supervise(args, argv) -> int:
     t_begin = time.time()
     budget_s = float(os.environ.get("B200ZERO_BENCH_BUDGET_S", "800"))
     startup_s = float(os.environ.get("B200ZERO_BENCH_STARTUP_S", "200"))      # no progress mark / stuck in rendezvous
-    quiet_s = float(os.environ.get("B200ZERO_BENCH_QUIET_S", str(75 + args.steps)))   # between two marks once steps run
+    quiet_s = float(os.environ.get("B200ZERO_BENCH_QUIET_S", str(45 + 2 * args.steps)))   # between two marks once steps run
     sign = 1 if base_port + 227 < 65000 else -1             # stay inside the valid port range
     attempts = [("primary", list(argv), base_port + sign * 113)]
-    if args.comm != "nccl" and args.impl != "nccl":
+    if args.comm != "nccl" and args.impl not in ("nccl", "torch"):
+        # the fused path once more (an 8-GPU run that stalls does so at a random step), then NCCL
+        attempts.append(("fused-retry", list(argv) + ["--retry-note", "the first attempt of this run made no progress or "
+                         "failed and was stopped by the supervisor; this line is the second attempt, same settings"],
+                         base_port + sign * 170))
         attempts.append(("nccl-fallback", list(argv) + ["--comm", "nccl", "--fallback-note",
                          "the default (fused-collective) run made no progress or failed; this line was measured on NCCL "
                          "collectives with the same compute kernels"],
@@ -324,8 +330,8 @@ def supervise(args, argv) -> int:
         env = dict(os.environ, MASTER_PORT=str(port), B200ZERO_HEARTBEAT_FILE=hb, B200ZERO_BENCH_RESULT_FILE=park)
         env.pop("TORCHELASTIC_USE_AGENT_STORE", None)      # the children rendezvous on their own store
         t0 = time.time()
-        last_attempt = name == attempts[-1][0]
-        cutoff = t_begin + (budget_s if last_attempt else 0.55 * budget_s)
+        share = {1: [1.0], 2: [0.55, 1.0], 3: [0.35, 0.65, 1.0]}[len(attempts)][[a[0] for a in attempts].index(name)]
+        cutoff = t_begin + share * budget_s
         p = child["p"] = subprocess.Popen([sys.executable, os.path.abspath(__file__), "--worker"] + av, env=env)
         verdict = None
         while verdict is None:
@@ -648,6 +654,8 @@ def run_ours(args) -> int:
         out["config"]["env_switches"] = opt_ins          # which non-default kernels / schedules this run used
     if args.fallback_note:
         out["fallback"] = args.fallback_note
+    if args.retry_note:
+        out["retried"] = args.retry_note
     if breakdown is not None:
         out["breakdown_ms"] = {k: round(v, 2) for k, v in breakdown.items()}
     if e2e_ms is not None:
@@ -729,7 +737,7 @@ def _fake_worker(args) -> int:
     beat("pg")
     beat("engine")
     if args.comm != "nccl":
-        if mode == "hang":
+        if mode == "hang" or (mode == "hang-once" and not args.retry_note):
             time.sleep(3600)
         if mode == "crash" and rank == world - 1:
             return 7
@@ -740,6 +748,8 @@ def _fake_worker(args) -> int:
     out = {"metric": METRIC, "value": 1.0, "fake": mode, "comm": args.comm}
     if args.fallback_note:
         out["fallback"] = args.fallback_note
+    if args.retry_note:
+        out["retried"] = args.retry_note
     if mode == "probe-hang":          # timed regions done, result parked, then the spike-to-halt probe never returns
         park = os.environ.get("B200ZERO_BENCH_RESULT_FILE")
         if park and rank == 0:
