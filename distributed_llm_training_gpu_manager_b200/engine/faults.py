@@ -7,6 +7,8 @@ which is what a transient hardware fault looks like.
     B200ZERO_INJECT_NAN_GRAD_AT=<step>           poison one gradient element with NaN
     B200ZERO_KILL_RANK_AT=<step>:<rank>          SIGKILL that rank at the top of the step
     B200ZERO_PREEMPT_AT=<step>                   deliver SIGTERM to self (spot preemption)
+    B200ZERO_HANG_AT=<step>:<rank>               that rank stops at the top of the step and never returns (a rank
+                                                 stuck inside a collective); first start only, like the kill
 """
 from __future__ import annotations
 
@@ -25,6 +27,8 @@ class FaultPlan:
     kill_at: Optional[int] = None
     kill_rank: int = 0
     preempt_at: Optional[int] = None
+    hang_at: Optional[int] = None
+    hang_rank: int = 0
     on_inject: Optional[Callable] = None    # called right after a mid-backward fault was written (probes timestamp it)
     fired: Set[str] = field(default_factory=set)
 
@@ -45,6 +49,10 @@ class FaultPlan:
         v = env.get("B200ZERO_PREEMPT_AT")
         if v:
             p.preempt_at = int(v)
+        v = env.get("B200ZERO_HANG_AT")
+        if v:
+            a, _, b = v.partition(":")
+            p.hang_at, p.hang_rank = int(a), int(b or 0)
         return p
 
     def _once(self, key: str) -> bool:
@@ -91,6 +99,11 @@ class FaultPlan:
         if self.kill_at == step and engine.rank == self.kill_rank and self._once(f"kill{step}") \
                 and os.environ.get("B200ZERO_RESTART_COUNT", "0") == "0":
             os.kill(os.getpid(), signal.SIGKILL)
+        if self.hang_at == step and engine.rank == self.hang_rank and self._once(f"hang{step}") \
+                and os.environ.get("B200ZERO_RESTART_COUNT", "0") == "0":
+            import time
+            while True:                      # the other ranks now wait for this one inside their next collective
+                time.sleep(3600)
         if self.preempt_at == step and self._once(f"preempt{step}") \
                 and os.environ.get("B200ZERO_RESTART_COUNT", "0") == "0":
             os.kill(os.getpid(), signal.SIGTERM)

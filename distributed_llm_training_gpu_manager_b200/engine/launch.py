@@ -10,16 +10,27 @@ It is also the **supervisor** the reference lacks: it keeps th
 forwards SIGTERM (emergency checkpoint), and when any rank dies abnormally it tears the others
 down and — with ``--max_restarts`` — relaunches the whole job, which resumes from the newest
 verified checkpoint (rank failure → detect → roll back → resume).
+
+A job can also stop without anybody dying: a lost peer leaves the other ranks waiting inside a
+collective (the fused kernels poll peer flags; NCCL kernels poll too). ``--stall_timeout S`` makes
+every engine touch a per-rank heartbeat file after each optimizer step (``B200ZERO_HEARTBEAT_DIR``,
+``ZeroEngine._optimizer_step``); when no rank has completed a step for ``S`` seconds the job is torn
+down and relaunched like after a crash, and — ``--stall_fallback nccl``, the default — the relaunched
+workers run on NCCL collectives (``B200ZERO_COMM=nccl``).
 """
 from __future__ import annotations
 
 import argparse
 import os
+import shutil
 import signal
 import subprocess
 import sys
+import tempfile
 import time
-from typing import List
+from typing import List, Optional
+
+STALLED = 124          # exit code of a job that was torn down because it stopped making progress
 
 PKG = (__package__ or __name__).split(".")[0]
 
@@ -34,6 +45,13 @@ def parse(argv: List[str]) -> argparse.Namespace:
     ap.add_argument("--max_restarts", type=int, default=int(os.environ.get("B200ZERO_MAX_RESTARTS", "0")))
     ap.add_argument("--backend", default=os.environ.get("B200ZERO_BACKEND", "auto"))
     ap.add_argument("--placement", default="topology", choices=["topology", "linear"])
+    ap.add_argument("--stall_timeout", type=float, default=float(os.environ.get("B200ZERO_STALL_TIMEOUT", "0")),
+                    help="seconds without a completed optimizer step on any rank before the job counts as stalled "
+                         "(0 = no stall detection); the first step gets this long plus --stall_startup")
+    ap.add_argument("--stall_startup", type=float, default=float(os.environ.get("B200ZERO_STALL_STARTUP", "600")),
+                    help="extra time allowed before the first heartbeat (model build, rendezvous, checkpoint load)")
+    ap.add_argument("--stall_fallback", default=os.environ.get("B200ZERO_STALL_FALLBACK", "nccl"),
+                    choices=["none", "nccl"], help="after a stall, relaunch on NCCL collectives (default) or unchanged")
     ap.add_argument("script")
     ap.add_argument("script_args", nargs=argparse.REMAINDER)
     return ap.parse_args(argv)
@@ -51,7 +69,7 @@ def _devices_for(n: int, placement: str) -> List[int]:
     return list(range(n))
 
 
-def _spawn(ns: argparse.Namespace, restart: int) -> List[subprocess.Popen]:
+def _spawn(ns: argparse.Namespace, restart: int, extra_env: Optional[dict] = None) -> List[subprocess.Popen]:
     world = ns.num_gpus * ns.num_nodes
     addr = "127.0.0.1" if ns.master_addr == "localhost" else ns.master_addr
     devices = _devices_for(ns.num_gpus, ns.placement)
@@ -61,7 +79,7 @@ def _spawn(ns: argparse.Namespace, restart: int) -> List[subprocess.Popen]:
         env = dict(os.environ, RANK=str(rank), LOCAL_RANK=str(local), WORLD_SIZE=str(world), MASTER_ADDR=addr,
                    MASTER_PORT=str(ns.master_port + restart), LOCAL_WORLD_SIZE=str(ns.num_gpus),
                    B200ZERO_RESTART_COUNT=str(restart), B200ZERO_BACKEND=ns.backend,
-                   B200ZERO_DEVICE=str(devices[local]))
+                   B200ZERO_DEVICE=str(devices[local]), **(extra_env or {}))
         if "OMP_NUM_THREADS" not in env:  # N ranks x all cores oversubscribes the host badly
             env["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 1) // max(ns.num_gpus, 1)))
         if ns.script.startswith("builtin:"):
@@ -73,10 +91,44 @@ def _spawn(ns: argparse.Namespace, restart: int) -> List[subprocess.Popen]:
     return procs
 
 
-def _supervise(procs: List[subprocess.Popen], term_flag: List[bool]) -> int:
-    """Wait for all ranks; on the first abnormal exit kill the rest. Returns the job's exit code."""
+def _teardown(procs: List[subprocess.Popen], hard: bool = False) -> None:
+    for p in procs:
+        if p.poll() is None:
+            p.kill() if hard else p.terminate()
+    deadline = time.time() + 10
+    for p in procs:
+        try:
+            p.wait(timeout=max(0.1, deadline - time.time()))
+        except subprocess.TimeoutExpired:
+            p.kill()
+
+
+def newest_heartbeat(hb_dir: str) -> Optional[float]:
+    """mtime of the most recent per-rank heartbeat file, None before the first one."""
+    try:
+        times = [os.path.getmtime(os.path.join(hb_dir, f)) for f in os.listdir(hb_dir)]
+    except OSError:
+        return None
+    return max(times) if times else None
+
+
+def _supervise(procs: List[subprocess.Popen], term_flag: List[bool], hb_dir: Optional[str] = None,
+               stall_timeout: float = 0.0, stall_startup: float = 600.0) -> int:
+    """Wait for all ranks; on the first abnormal exit kill the rest. Returns the job's exit code
+    (``STALLED`` when the job was stopped because no rank completed a step for ``stall_timeout`` seconds)."""
     forwarded = False
+    t0 = time.time()
     while True:
+        if stall_timeout > 0 and hb_dir and not term_flag[0]:
+            last = newest_heartbeat(hb_dir)
+            now = time.time()
+            quiet = now - last if last is not None else now - t0 - stall_startup
+            if quiet > stall_timeout:
+                print(f"[launch] no rank has completed a step for {quiet:.0f} s "
+                      f"({'since the first heartbeat' if last is not None else 'and none ever did'}): "
+                      f"stopping the job", flush=True)
+                _teardown(procs, hard=True)      # a rank that waits inside a kernel does not react to SIGTERM
+                return STALLED
         if term_flag[0] and not forwarded:
             for p in procs:
                 if p.poll() is None:
@@ -85,15 +137,7 @@ def _supervise(procs: List[subprocess.Popen], term_flag: List[bool]) -> int:
         codes = [p.poll() for p in procs]
         bad = [c for c in codes if c not in (None, 0)]
         if bad:
-            for p in procs:
-                if p.poll() is None:
-                    p.terminate()
-            deadline = time.time() + 10
-            for p in procs:
-                try:
-                    p.wait(timeout=max(0.1, deadline - time.time()))
-                except subprocess.TimeoutExpired:
-                    p.kill()
+            _teardown(procs)
             return bad[0]
         if all(c == 0 for c in codes):
             return 0
@@ -105,14 +149,25 @@ def main(argv: List[str] = None) -> int:
     term = [False]
     signal.signal(signal.SIGTERM, lambda *_: term.__setitem__(0, True))
     restart = 0
+    extra_env: dict = {}
     while True:
-        procs = _spawn(ns, restart)
-        rc = _supervise(procs, term)
+        hb_dir = tempfile.mkdtemp(prefix="b200zero_hb_") if ns.stall_timeout > 0 else None
+        if hb_dir:
+            extra_env["B200ZERO_HEARTBEAT_DIR"] = hb_dir
+        procs = _spawn(ns, restart, extra_env)
+        try:
+            rc = _supervise(procs, term, hb_dir, ns.stall_timeout, ns.stall_startup)
+        finally:
+            if hb_dir:
+                shutil.rmtree(hb_dir, ignore_errors=True)
         if rc == 0 or term[0] or restart >= ns.max_restarts:
             return rc
         restart += 1
-        print(f"[launch] job failed with exit code {rc}; restart {restart}/{ns.max_restarts} "
-              f"(workers resume from the newest verified checkpoint)", flush=True)
+        if rc == STALLED and ns.stall_fallback == "nccl":
+            extra_env["B200ZERO_COMM"] = "nccl"
+        print(f"[launch] job {'stalled' if rc == STALLED else f'failed with exit code {rc}'}; restart "
+              f"{restart}/{ns.max_restarts} (workers resume from the newest verified checkpoint"
+              f"{', on NCCL collectives' if extra_env.get('B200ZERO_COMM') == 'nccl' else ''})", flush=True)
 
 
 if __name__ == "__main__":

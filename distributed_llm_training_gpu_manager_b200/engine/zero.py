@@ -184,6 +184,8 @@ class ZeroEngine:
         # Set by whoever learns that this rank is about to lose its machine (SIGTERM handler, spot probe). The bit rides
         # in the per-step stats all-reduce, so every rank sees the same answer at the same step boundary.
         self.preempt_requested = False
+        hb_dir = os.environ.get("B200ZERO_HEARTBEAT_DIR")
+        self._heartbeat_path = os.path.join(hb_dir, f"rank{self.rank}") if hb_dir else None
         self._prefetch_evt: Dict[int, Any] = {}
 
         # ---- parameters, units, layout ----
@@ -701,6 +703,12 @@ class ZeroEngine:
             self._loss_accum.zero_()
         self.global_steps += 1
         self.schedule.last_step = self.global_steps
+        if self._heartbeat_path:                 # the launcher's stall detection watches this file (engine/launch.py)
+            try:
+                with open(self._heartbeat_path, "w") as f:
+                    f.write(str(self.global_steps))
+            except OSError:
+                pass
         m = {"step": self.global_steps, "loss": vals[2], "grad_norm": vals[3], "grad_norm_sq": vals[3] ** 2,
              "nonfinite": overflow, "lr": lr, "loss_scale": self.scaler.scale, "skipped": overflow,
              "preempt": vals[4] > 0}

@@ -2,6 +2,7 @@
 asynchronous saves, vector-granular segment tables."""
 import os
 import threading
+from pathlib import Path
 import time
 
 import pytest
@@ -215,3 +216,35 @@ def test_segment_table_packs_partitioned_and_push_into_one_word():
     flags = t[:, 3].tolist()
     assert [f & 0xFFFFFFFF for f in flags] == [1, 0, 1]          # int32 partitioned (low half, little endian)
     assert [f >> 32 for f in flags] == [0, 1, 1]                  # int32 push (high half)
+
+
+# ---------------------------------------------------------------- a job that stops without anybody dying
+def test_launcher_detects_a_stalled_job_and_relaunches_it(tmp_path):
+    """Rank 1 stops at the top of step 12 and never returns (first start only); rank 0 then waits for it inside its
+    next collective. Nobody dies, so only the heartbeat can tell: the launcher stops the job after the stall window,
+    relaunches it, the workers resume from the newest verified checkpoint and finish."""
+    import json
+    import subprocess
+    import sys
+    from dist_utils import free_port
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    cfg_path = tmp_path / "ds.json"
+    cfg_path.write_text(json.dumps(DeepSpeedLauncher().generate_config(DeepSpeedConfig(
+        zero_stage=2, offload_optimizer="none", offload_param="none", fp16_enabled=False, bf16_enabled=False,
+        train_micro_batch_size_per_gpu=4, gradient_accumulation_steps=1, learning_rate=3e-3, warmup_steps=5,
+        total_training_steps=200, wall_clock_breakdown=False))))
+    result = tmp_path / "result.json"
+    env = dict(os.environ, B200ZERO_BACKEND="gloo", B200ZERO_HANG_AT="12:1", MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="2")
+    res = subprocess.run(
+        [sys.executable, "-m", "distributed_llm_training_gpu_manager_b200.engine.launch", "--num_gpus=2",
+         f"--master_port={free_port()}", "--max_restarts=1", "--stall_timeout=8", "--stall_startup=240",
+         "--placement=linear", "builtin:gpt2-tiny", f"--deepspeed_config={cfg_path}", "--steps=25",
+         f"--save_dir={tmp_path / 'ckpt'}", "--save_every=5", f"--result={result}", "--seq_len=32", "--window=20"],
+        env=env, capture_output=True, text=True, timeout=600, cwd=str(Path(__file__).resolve().parent.parent))
+    log = res.stdout + res.stderr
+    assert res.returncode == 0, log[-3000:]
+    assert "no rank has completed a step" in log and "job stalled; restart 1/1" in log, log[-3000:]
+    assert "on NCCL collectives" in log                      # the relaunch is asked to leave the fused collectives
+    assert "resumed from global_step10" in log, log[-3000:]
+    out = json.loads(result.read_text())
+    assert out["status"] == "finished" and out["final_step"] == 25
