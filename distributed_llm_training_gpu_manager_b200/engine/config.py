@@ -91,6 +91,32 @@ class EngineConfig:
         return self.micro_batch * self.grad_accum * world_size
 
 
+def audit(c: EngineConfig, unit_numels=(), world_size: int = 1, fused: bool = False) -> list:
+    """What this engine does with the keys of the emitted config that have no literal counterpart here
+    (ref ``deepspeed_launcher.py:133-142,186-194``). Returns human-readable notes; the engine logs them once.
+    Keys that change arithmetic or traffic are honoured in the engine itself (``reduce_scatter``,
+    ``prescale_gradients`` / ``gradient_predivide_factor``, ``stage3_*``, ``sub_group_size``, offload blocks)."""
+    notes = []
+    biggest = max(unit_numels, default=0)
+    if c.stage >= 2 and biggest > c.reduce_bucket_size:
+        notes.append(f"reduce_bucket_size={c.reduce_bucket_size}: gradients are reduced one unit (transformer block) at a "
+                     f"time and the largest unit has {biggest} elements; the unit is not split further")
+    if c.stage >= 1 and c.stage <= 2 and biggest > c.allgather_bucket_size:
+        notes.append(f"allgather_bucket_size={c.allgather_bucket_size}: updated rows are gathered one unit at a time "
+                     f"(largest: {biggest} elements)")
+    if not c.contiguous_gradients:
+        notes.append("contiguous_gradients=false: gradients always live in flat per-unit buffers here; nothing to turn off")
+    if not c.reduce_scatter and c.stage >= 1 and world_size > 1:
+        notes.append("reduce_scatter=false: gradients are all-reduced and every rank keeps its rows; the fused backend "
+                     "(which always reduce-scatters) is not used for this job")
+    if (c.prescale_gradients or c.predivide_factor != 1.0) and fused:
+        notes.append("prescale_gradients / gradient_predivide_factor: the fused reduce kernel sums in fp32 and scales "
+                     "once afterwards, so there is nothing to pre-scale; honoured on the NCCL / gloo path")
+    if c.stage >= 3 and c.prefetch_bucket_size <= 0:
+        notes.append("stage3_prefetch_bucket_size=0: blocks are gathered synchronously, on demand")
+    return notes
+
+
 def load_config(src: Union[str, Dict[str, Any], EngineConfig]) -> EngineConfig:
     if isinstance(src, EngineConfig):
         return src

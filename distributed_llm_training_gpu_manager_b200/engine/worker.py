@@ -106,7 +106,8 @@ def main(argv=None) -> int:
         eval_batches = token_batches(ns.eval_data, ecfg.micro_batch, seq, device, rank, world, seed=ns.seed + 1,
                                      shuffle=False, dtype=ns.data_dtype, vocab_size=mcfg.vocab_size, prefetch=0)
     tcfg = TrainerConfig(total_steps=ns.steps, save_dir=ns.save_dir, save_every=ns.save_every,
-                         metrics_path=ns.metrics, monitor=MonitorConfig(window_size=ns.window), log_every=10,
+                         metrics_path=ns.metrics, monitor=MonitorConfig(window_size=ns.window),
+                         log_every=min(10, max(1, ecfg.steps_per_print)),   # steps_per_print caps the log interval
                          eval_batches=eval_batches, eval_every=ns.eval_every, eval_steps=ns.eval_steps)
     res = Trainer(engine, batches, tcfg).run()
     if rank == 0 and ns.result:

@@ -166,12 +166,14 @@ class ZeroEngine:
         # "auto" prefers the fused peer-memory kernels (the product) and falls back to NCCL (the baseline)
         # when peers cannot be mapped (no P2P/IPC) or the dtype is not bf16
         self._want_fused = (comm in ("fused", "auto") and self.on_cuda and self.world_size > 1
+                            and self.cfg.reduce_scatter                  # reduce_scatter: false asks for all-reduce
                             and self.cfg.compute_dtype == torch.bfloat16
                             and self.cfg.offload_optimizer == "none"     # K3 updates device-resident state
                             and self.cfg.offload_param == "none"         # K2 / pull gather read device-resident shards
                             and os.environ.get("B200ZERO_COMM", comm) != "nccl")
         if comm in ("fused", "auto") and self.on_cuda and self.world_size > 1 and not self._want_fused:
-            why = ("compute dtype is not bf16" if self.cfg.compute_dtype != torch.bfloat16 else
+            why = ("reduce_scatter is false" if not self.cfg.reduce_scatter else
+                   "compute dtype is not bf16" if self.cfg.compute_dtype != torch.bfloat16 else
                    "optimizer state is offloaded" if self.cfg.offload_optimizer != "none" else
                    "parameters are offloaded" if self.cfg.offload_param != "none" else "B200ZERO_COMM=nccl")
             _log.warning("fused peer-memory collectives declined (%s): this job runs on NCCL collectives", why)
@@ -227,6 +229,12 @@ class ZeroEngine:
                 self.fused = FusedComm(self)
             else:
                 self.comm_mode = "nccl" if self.on_cuda else "gloo"  # single rank / CPU: nothing to fuse
+        from .config import audit
+        self.config_notes = audit(self.cfg, [u.full_numel for u in self.layout.units], self.world_size,
+                                  fused=self.fused is not None)
+        if self.rank == 0:
+            for note in self.config_notes:
+                _log.warning("config: %s", note)
 
     # ------------------------------------------------------------------ buffers
     def _slice_rows(self, spec: ParamSpec, full: torch.Tensor) -> torch.Tensor:
@@ -534,6 +542,12 @@ class ZeroEngine:
                 pass
             else:
                 rdt = self.cfg.reduce_dtype
+                # prescale_gradients / gradient_predivide_factor (ref deepspeed_launcher.py:141-142 emits the keys):
+                # divide before the low-precision sum so it cannot overflow, finish the mean afterwards
+                pre = float(self.cfg.predivide_factor) if self.cfg.prescale_gradients else 1.0
+                if self.cfg.prescale_gradients and pre == 1.0:
+                    pre = float(self.world_size)
+                post = scale * pre
                 for spec in u.params:
                     g = gb[spec.full_offset:spec.full_offset + spec.numel]
                     dst = self.shard_grads[spec.shard_offset:spec.shard_offset + spec.shard_numel]
@@ -541,11 +555,20 @@ class ZeroEngine:
                         dst.add_(g.to(dst.dtype))
                         continue
                     gr = g if g.dtype == rdt else g.to(rdt)
-                    if spec.partitioned:
-                        dst.add_(_reduce_scatter(gr, self.rank, self.world_size).to(dst.dtype), alpha=scale)
+                    if pre != 1.0:
+                        gr = gr / pre
+                    if spec.partitioned and self.cfg.reduce_scatter:
+                        dst.add_(_reduce_scatter(gr, self.rank, self.world_size).to(dst.dtype), alpha=post)
+                    elif spec.partitioned:            # reduce_scatter: false -> all-reduce, then keep my rows
+                        full = gr.clone() if gr.data_ptr() == g.data_ptr() else gr
+                        dist.all_reduce(full)
+                        n = spec.shard_numel
+                        dst.add_(full[self.rank * n:(self.rank + 1) * n].to(dst.dtype), alpha=post)
                     else:
+                        if gr.data_ptr() == g.data_ptr():
+                            gr = gr.clone()
                         dist.all_reduce(gr)
-                        dst.add_(gr.to(dst.dtype), alpha=scale)
+                        dst.add_(gr.to(dst.dtype), alpha=post)
             if getattr(self, "_zero_after_reduce", True):
                 gb.zero_()         # autograd accumulates in place; the native executor overwrites instead
             if use_side and self.pooled_grads and ui >= 1:

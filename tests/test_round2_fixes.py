@@ -248,3 +248,36 @@ def test_launcher_detects_a_stalled_job_and_relaunches_it(tmp_path):
     assert "resumed from global_step10" in log, log[-3000:]
     out = json.loads(result.read_text())
     assert out["status"] == "finished" and out["final_step"] == 25
+
+
+# ---------------------------------------------------------------- emitted keys that used to be parsed and dropped
+def _keys_rank(rank, world, overrides):
+    d = ds_dict(2)
+    d["zero_optimization"].update(overrides.get("zero", {}))
+    d.update(overrides.get("top", {}))
+    eng = initialize(_model(), d, device="cpu")
+    data = synthetic_batches(VOCAB, MB, SEQ, "cpu", rank, world)
+    losses = []
+    for _ in range(4):
+        eng.backward(eng(*data(eng.micro_steps)))
+        losses.append(eng.step()["loss"])
+    return losses, eng.config_notes
+
+
+def test_reduce_scatter_false_and_prescale_are_honoured_and_equivalent():
+    base = run_ranks(_keys_rank, 2, ({},))
+    allred = run_ranks(_keys_rank, 2, ({"zero": {"reduce_scatter": False}},))
+    presc = run_ranks(_keys_rank, 2, ({"top": {"prescale_gradients": True, "gradient_predivide_factor": 2.0}},))
+    for (l0, n0), (l1, n1), (l2, _n2) in zip(base, allred, presc):
+        assert l1 == pytest.approx(l0, rel=1e-5) and l2 == pytest.approx(l0, rel=1e-5)
+        assert not n0 and any("reduce_scatter=false" in n for n in n1)
+
+
+def test_config_audit_names_what_is_fixed_here():
+    from distributed_llm_training_gpu_manager_b200.engine.config import audit, load_config
+    d = ds_dict(2)
+    d["zero_optimization"].update(reduce_bucket_size=1000, allgather_bucket_size=1000, contiguous_gradients=False)
+    notes = audit(load_config(d), unit_numels=[5000, 70000], world_size=2)
+    assert len(notes) == 3 and "reduce_bucket_size=1000" in notes[0] and "70000" in notes[0]
+    assert "allgather_bucket_size" in notes[1] and "contiguous_gradients" in notes[2]
+    assert audit(load_config(ds_dict(3)), unit_numels=[5000], world_size=2) == []
