@@ -11,9 +11,9 @@
 // B (= W) is consumed MN-major straight from the row-major weight: no transposed copy of W exists anywhere.
 //
 // Each weight is used exactly once in backward (by its dgrad) when nothing is recomputed, so with this kernel the
-// backward pass needs no bulk gather and no prefetch stream. Status: written after this round's GPU time was spent;
-// checked on emulated ranks by tests/test_ag_gemm.py::test_ag_gemm_dgrad_emulated_ranks (child process); the engine
-// still uses the prefetched pull all-gather + plain GEMM until this has run on hardware.
+// backward pass needs no bulk gather and no prefetch stream. Validated on B200 (emulated ranks and inside the
+// engine on 2 GPUs); end to end it measured 1–3 % slower than prefetched pull gathers + plain GEMMs (2 and 8 GPUs), so
+// the engine uses it only with B200ZERO_AG_DGRAD=1.
 #include "common.cuh"
 #include "../include/b200zero.h"
 

@@ -207,7 +207,7 @@ class NativeLlamaEngine(ZeroEngine):
         self._ag_fused = (self.fused is not None and self.stage >= 3 and self.pooled_params
                           and os.environ.get("B200ZERO_AG_GEMM", "1") == "1")
         self._ag_ptrs: Dict[str, Any] = {}
-        # K2 dgrad flavour (opt-in until it has run on hardware): with nothing recomputed every weight is used
+        # K2 dgrad flavour (opt-in: validated, but 1-3 % slower end to end): with nothing recomputed every weight is used
         # exactly once in backward — by its dgrad — so that GEMM gathers it in-kernel and backward needs no
         # bulk gather / prefetch stream at all.
         self._ag_dgrad = (self._ag_fused and self.recompute in ("none", "light")
