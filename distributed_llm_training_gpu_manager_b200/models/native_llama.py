@@ -85,7 +85,7 @@ def activation_bytes(c: ModelConfig, micro_batch: int, seq_len: int, head_chunk:
 
 
 def static_bytes(c: ModelConfig, world_size: int, stage: int = 3, offload_optimizer: bool = False,
-                 grad_bytes: int = 2) -> Dict[str, float]:
+                 grad_bytes: int = 2, offload_param: bool = False, param_slots: int = 2) -> Dict[str, float]:
     """Per-GPU bytes of the engine's persistent buffers (ZeRO-3 native path), for capacity planning
     against 180 GB of HBM3e (BASELINE.json config 5: Llama-3-70B on 8 × B200)."""
     d, hd = c.hidden, c.head_dim
@@ -94,11 +94,16 @@ def static_bytes(c: ModelConfig, world_size: int, stage: int = 3, offload_optimi
     root = 2 * c.padded_vocab * d + d
     total = c.n_layers * block + root
     shard = total / max(world_size, 1) if stage >= 1 else total
-    out = {"optimizer_states": 0.0 if offload_optimizer else 12.0 * shard, "param_shard": 2.0 * shard,
+    # offload_param: the 16-bit shard lives in pinned host memory; the device keeps one staging buffer per resident
+    # block plus one for the root unit (a unit's rows of the shard)
+    staging = 2.0 * (param_slots * block + root) / max(world_size, 1)
+    out = {"optimizer_states": 0.0 if offload_optimizer else 12.0 * shard,
+           "param_shard": staging if (offload_param and stage >= 3) else 2.0 * shard,
            "grad_shard": float(grad_bytes) * shard,
-           "param_buffers": 2.0 * (2 * block + root) if stage >= 3 else 2.0 * total,
+           "param_buffers": 2.0 * (max(param_slots, 2) * block + root) if stage >= 3 else 2.0 * total,
            "grad_buffers": 2.0 * (2 * block + root) if stage >= 2 else 2.0 * total,
-           "host_pinned": 12.0 * shard if offload_optimizer else 0.0, "params_total": float(total)}
+           "host_pinned": (12.0 * shard if offload_optimizer else 0.0) + (2.0 * shard if offload_param else 0.0),
+           "params_total": float(total)}
     out["device_total"] = sum(v for k, v in out.items() if k not in ("host_pinned", "params_total"))
     return out
 

@@ -281,3 +281,15 @@ def test_config_audit_names_what_is_fixed_here():
     assert len(notes) == 3 and "reduce_bucket_size=1000" in notes[0] and "70000" in notes[0]
     assert "allgather_bucket_size" in notes[1] and "contiguous_gradients" in notes[2]
     assert audit(load_config(ds_dict(3)), unit_numels=[5000], world_size=2) == []
+
+
+def test_capacity_planner_knows_parameter_offload_and_resident_blocks():
+    from distributed_llm_training_gpu_manager_b200.models import get_config
+    from distributed_llm_training_gpu_manager_b200.models.native_llama import static_bytes
+    c70 = get_config("llama3-70b")
+    base = static_bytes(c70, 8, offload_optimizer=True)
+    both = static_bytes(c70, 8, offload_optimizer=True, offload_param=True)
+    assert both["param_shard"] < 0.1 * base["param_shard"]            # only the staging buffers stay on the device
+    assert both["host_pinned"] - base["host_pinned"] == pytest.approx(2.0 * c70.num_params() / 8, rel=0.02)
+    wide = static_bytes(c70, 8, offload_optimizer=True, param_slots=4)
+    assert wide["param_buffers"] > base["param_buffers"] and wide["device_total"] > base["device_total"]
