@@ -30,3 +30,19 @@ def test_fleet_topology_and_selection_on_mocks(capsys):
     assert topo["node_type"].startswith("HGX B200") and len(topo["links_per_gpu"]) == 8
     assert _run(capsys, "select", "--count", "1", "--mock")["selected"] == [0]
     assert _run(capsys, "select", "--count", "2", "--mock")["selected"] == []      # GPU 1 is over its memory threshold
+
+
+def test_doctor_reports_every_check_and_an_overall_verdict():
+    import json
+    import subprocess
+    import sys
+    res = subprocess.run([sys.executable, "-m", "distributed_llm_training_gpu_manager_b200", "doctor", "--gpus", "2"],
+                         capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stderr[-1500:]
+    out = json.loads(res.stdout)
+    assert set(out) == {"ready", "checks"}
+    for name in ("kernel_library", "cuda_devices", "host_memory", "memlock_limit", "cpu_cores"):
+        assert {"ok", "detail", "needed_for_default_job"} <= set(out["checks"][name]), name
+    import torch
+    if not torch.cuda.is_available():
+        assert out["ready"] is False and out["checks"]["cuda_devices"]["detail"]["wanted"] == 2
