@@ -525,6 +525,8 @@ def run_ours(args) -> int:
     wd_s = float(os.environ.get("B200ZERO_BENCH_WATCHDOG_S", "0") or 0)
     if wd_s > 0:
         import faulthandler
+        if getattr(engine, "fused", None) is not None:
+            engine.fused.prepare_debug_snapshot()      # pinned buffer + stream made now, while the device is healthy
 
         def _watch():
             fired = False

@@ -205,9 +205,9 @@ class FusedComm:
         """What this rank's signal pad and host-side epoch counters look like right now, read on a private stream
         (works while the main / communication streams are stuck behind a kernel that waits for a peer). For every
         channel and phase: the epoch each rank has announced to us. Used by bench.py's stall watchdog."""
-        side = torch.cuda.Stream(device=self.e.device)
-        words = self.L.bz_comm_signal_pad_bytes() // 4
-        host = torch.zeros(words, dtype=torch.int32).pin_memory()
+        self.prepare_debug_snapshot()
+        side, host = self._dbg_stream, self._dbg_host
+        words = host.numel()
         with torch.cuda.stream(side):
             host.copy_(self.signal.tensor(torch.int32, words), non_blocking=True)
         side.synchronize()
@@ -220,6 +220,13 @@ class FusedComm:
                 pad[f"{nm}.phase{ph}"] = [v & 0xFFFFFFFF for v in tab[base:base + ws]]
         return {"rank": self.e.rank, "host_epochs": {names[k]: v for k, v in self.epoch.items()}, "announced_to_me": pad,
                 "k1_launches": self.launches}
+
+    def prepare_debug_snapshot(self) -> None:
+        """Create the stream and the pinned buffer ``debug_snapshot`` uses. Call it while the device is healthy: pinning
+        host memory can block behind a kernel that never finishes, which is exactly when the snapshot is wanted."""
+        if not hasattr(self, "_dbg_stream"):
+            self._dbg_stream = torch.cuda.Stream(device=self.e.device)
+            self._dbg_host = torch.zeros(self.L.bz_comm_signal_pad_bytes() // 4, dtype=torch.int32).pin_memory()
 
     def can_push_root(self) -> bool:
         import os
