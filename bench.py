@@ -553,6 +553,13 @@ def run_ours(args) -> int:
         beat(f"warmup{i}")
     sync_all()
 
+    # The cyclic garbage collector stays off from here to the end of the measured regions: a collection pause on one
+    # rank is a pause of the whole job (every rank waits for the slowest in each unit's reduce). Reference counting
+    # still frees every tensor at once; the few dozen steps of a run cannot accumulate cycles that matter.
+    import gc
+    gc.collect()
+    gc.disable()
+
     # ---- device-timed region: exactly K steps ----
     sampler = ClockSampler(local)
     sampler.start()
@@ -718,6 +725,7 @@ def run_ours(args) -> int:
                                  "a non-finite step is skipped on the device inside that same step")
             halt = rep
         out["spike_to_halt_ms"] = halt
+    gc.enable()
     if rank == 0:
         print(json.dumps(out), flush=True)
     beat("printed")
