@@ -213,6 +213,9 @@ class JobRecord(BaseModel):
     started_at: str = Field(default_factory=lambda: _utc_now().isoformat())
     finished_at: Optional[str] = None
     restarts: int = 0
+    heartbeat_dir: str = ""                        # every rank's engine writes its step number here after each optimizer step
+    last_step: Optional[int] = None                # newest optimizer step any rank has completed (filled in by get / list)
+    seconds_since_progress: Optional[float] = None
 
 
 class JobRegistry:
@@ -233,7 +236,7 @@ class JobRegistry:
         proc = subprocess.Popen(list(argv), stdout=logf, stderr=subprocess.STDOUT, env=env, start_new_session=True)
         logf.close()  # the child holds its own descriptor; nothing to drain, nothing to block on
         rec = JobRecord(job_id=job_id, pid=proc.pid, argv=list(argv), config_path=config_path,
-                        log_path=str(log_path), status="running")
+                        log_path=str(log_path), status="running", heartbeat_dir=env.get("B200ZERO_HEARTBEAT_DIR", ""))
         with self._lock:
             self._jobs[job_id] = rec
             self._procs[job_id] = proc
@@ -260,14 +263,36 @@ class JobRegistry:
         with self._lock:
             self._callbacks.setdefault(job_id, []).append(cb)
 
+    @staticmethod
+    def _with_progress(rec: JobRecord) -> JobRecord:
+        """Copy of ``rec`` with the newest completed step and the time since then, read from the heartbeat files."""
+        out = rec.model_copy()
+        try:
+            files = [os.path.join(rec.heartbeat_dir, f) for f in os.listdir(rec.heartbeat_dir)] if rec.heartbeat_dir else []
+        except OSError:
+            files = []
+        best, newest = None, None
+        for f in files:
+            try:
+                step = int(open(f).read().strip() or 0)
+                mtime = os.path.getmtime(f)
+            except (OSError, ValueError):
+                continue
+            best = step if best is None else max(best, step)
+            newest = mtime if newest is None else max(newest, mtime)
+        out.last_step = best
+        if newest is not None and rec.status == "running":
+            out.seconds_since_progress = round(max(0.0, time.time() - newest), 1)
+        return out
+
     def get(self, job_id: str) -> Optional[JobRecord]:
         with self._lock:
             rec = self._jobs.get(job_id)
-            return rec.model_copy() if rec else None
+            return self._with_progress(rec) if rec else None
 
     def list(self) -> List[JobRecord]:
         with self._lock:
-            return [r.model_copy() for r in self._jobs.values()]
+            return [self._with_progress(r) for r in self._jobs.values()]
 
     def stop(self, job_id: str, sig: int = signal.SIGTERM, grace_s: float = 30.0) -> Optional[JobRecord]:
         """SIGTERM the job's process group (workers take an emergency checkpoint on
@@ -452,6 +477,10 @@ class DeepSpeedLauncher:
             pkg_parent = str(Path(__file__).resolve().parents[2])
             env["PYTHONPATH"] = pkg_parent + (os.pathsep + env["PYTHONPATH"] if env.get("PYTHONPATH") else "")
         try:
+            # progress of the job (newest completed optimizer step) is visible through the registry and the jobs API
+            hb_dir = self.registry.log_dir / f"{job_id}.hb"
+            hb_dir.mkdir(parents=True, exist_ok=True)
+            env["B200ZERO_HEARTBEAT_DIR"] = str(hb_dir)
             rec = self.registry.spawn(job_id, argv, env, config_path)
             result.status = "launched"
             result.details.update(pid=rec.pid, log_path=rec.log_path, engine=self.engine)

@@ -151,14 +151,24 @@ def main(argv: List[str] = None) -> int:
     restart = 0
     extra_env: dict = {}
     while True:
-        hb_dir = tempfile.mkdtemp(prefix="b200zero_hb_") if ns.stall_timeout > 0 else None
+        # heartbeat files: in the directory the caller named (the job registry reads progress from it), else in a
+        # temporary one when stall detection is on
+        given = os.environ.get("B200ZERO_HEARTBEAT_DIR")
+        hb_dir = given or (tempfile.mkdtemp(prefix="b200zero_hb_") if ns.stall_timeout > 0 else None)
         if hb_dir:
+            os.makedirs(hb_dir, exist_ok=True)
+            for f in os.listdir(hb_dir):             # a relaunch starts with a clean slate: old marks are not progress
+                if f.startswith("rank") and f[4:].isdigit():
+                    try:
+                        os.unlink(os.path.join(hb_dir, f))
+                    except OSError:
+                        pass
             extra_env["B200ZERO_HEARTBEAT_DIR"] = hb_dir
         procs = _spawn(ns, restart, extra_env)
         try:
             rc = _supervise(procs, term, hb_dir, ns.stall_timeout, ns.stall_startup)
         finally:
-            if hb_dir:
+            if hb_dir and not given:
                 shutil.rmtree(hb_dir, ignore_errors=True)
         if rc == 0 or term[0] or restart >= ns.max_restarts:
             return rc

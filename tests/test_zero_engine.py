@@ -194,6 +194,7 @@ def test_supervisor_restarts_after_rank_kill_and_resumes(tmp_path):
         os.environ.clear(); os.environ.update(env_backup)
     log = launcher.registry.tail(res.job_id) or ""
     assert rec is not None and rec.returncode == 0, log
+    assert rec.last_step == 30 and rec.heartbeat_dir          # progress is visible through the registry (heartbeat files)
     assert "restart 1/2" in log and "resumed from global_step15" in log, log
     out = json.loads(result_file.read_text())
     assert out["status"] == "finished" and out["final_step"] == 30
