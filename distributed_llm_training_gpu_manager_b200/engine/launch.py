@@ -45,6 +45,10 @@ def parse(argv: List[str]) -> argparse.Namespace:
     ap.add_argument("--max_restarts", type=int, default=int(os.environ.get("B200ZERO_MAX_RESTARTS", "0")))
     ap.add_argument("--backend", default=os.environ.get("B200ZERO_BACKEND", "auto"))
     ap.add_argument("--placement", default="topology", choices=["topology", "linear"])
+    ap.add_argument("--bind_cores", default=os.environ.get("B200ZERO_BIND_CORES", "none"), choices=["none", "even", "numa"],
+                    help="CPU affinity of the rank processes: even = the usable cores cut into one contiguous slice per "
+                         "rank; numa = the cores of the GPU's NUMA node shared between the ranks on that node. Keeps one "
+                         "rank's launch thread, host optimizer and data loader off another rank's cores")
     ap.add_argument("--stall_timeout", type=float, default=float(os.environ.get("B200ZERO_STALL_TIMEOUT", "0")),
                     help="seconds without a completed optimizer step on any rank before the job counts as stalled "
                          "(0 = no stall detection); the first step gets this long plus --stall_startup")
@@ -69,10 +73,60 @@ def _devices_for(n: int, placement: str) -> List[int]:
     return list(range(n))
 
 
+def _parse_cpulist(text: str) -> List[int]:
+    out: List[int] = []
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        a, _, b = part.partition("-")
+        out.extend(range(int(a), int(b or a) + 1))
+    return out
+
+
+def core_sets(n_ranks: int, mode: str, numa_of_rank: Optional[List[Optional[int]]] = None,
+              usable: Optional[List[int]] = None, node_cpus=None) -> List[Optional[List[int]]]:
+    """Cores for each local rank (None = leave the affinity alone). ``node_cpus(node) -> [cpu, ...]`` reads
+    /sys/devices/system/node/node<N>/cpulist by default."""
+    if mode == "none" or n_ranks < 1:
+        return [None] * n_ranks
+    usable = sorted(usable if usable is not None else os.sched_getaffinity(0))
+    if mode == "numa" and numa_of_rank and all(n is not None for n in numa_of_rank[:n_ranks]):
+        if node_cpus is None:
+            def node_cpus(node):
+                try:
+                    with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+                        return _parse_cpulist(f.read())
+                except OSError:
+                    return []
+        out: List[Optional[List[int]]] = [None] * n_ranks
+        for node in sorted(set(numa_of_rank[:n_ranks])):
+            ranks = [r for r in range(n_ranks) if numa_of_rank[r] == node]
+            cpus = [c for c in node_cpus(node) if c in set(usable)]
+            per = len(cpus) // len(ranks)
+            if per < 1:
+                return core_sets(n_ranks, "even", usable=usable)
+            for i, r in enumerate(ranks):
+                out[r] = cpus[i * per:(i + 1) * per]
+        return out
+    per = len(usable) // n_ranks
+    if per < 1:
+        return [None] * n_ranks
+    return [usable[r * per:(r + 1) * per] for r in range(n_ranks)]
+
+
 def _spawn(ns: argparse.Namespace, restart: int, extra_env: Optional[dict] = None) -> List[subprocess.Popen]:
     world = ns.num_gpus * ns.num_nodes
     addr = "127.0.0.1" if ns.master_addr == "localhost" else ns.master_addr
     devices = _devices_for(ns.num_gpus, ns.placement)
+    numa = None
+    if ns.bind_cores == "numa":
+        try:
+            from ..parallel.topology import discover_topology
+            topo = discover_topology()
+            numa = [topo.numa[d] if d < len(topo.numa) else None for d in devices]
+        except Exception:
+            numa = None
+    cores = core_sets(ns.num_gpus, ns.bind_cores, numa)
     procs = []
     for local in range(ns.num_gpus):
         rank = ns.node_rank * ns.num_gpus + local
@@ -87,7 +141,10 @@ def _spawn(ns: argparse.Namespace, restart: int, extra_env: Optional[dict] = Non
         else:
             cmd = [sys.executable, ns.script]
         cmd += [f"--local_rank={local}"] + list(ns.script_args)
-        procs.append(subprocess.Popen(cmd, env=env))
+        mine = cores[local]
+        if mine and "OMP_NUM_THREADS" not in os.environ:
+            env["OMP_NUM_THREADS"] = str(len(mine))
+        procs.append(subprocess.Popen(cmd, env=env, preexec_fn=(lambda c=mine: os.sched_setaffinity(0, c)) if mine else None))
     return procs
 
 

@@ -293,3 +293,35 @@ def test_capacity_planner_knows_parameter_offload_and_resident_blocks():
     assert both["host_pinned"] - base["host_pinned"] == pytest.approx(2.0 * c70.num_params() / 8, rel=0.02)
     wide = static_bytes(c70, 8, offload_optimizer=True, param_slots=4)
     assert wide["param_buffers"] > base["param_buffers"] and wide["device_total"] > base["device_total"]
+
+
+def test_rank_core_sets_even_and_numa():
+    from distributed_llm_training_gpu_manager_b200.engine.launch import _parse_cpulist, core_sets
+    assert _parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    assert core_sets(4, "none") == [None] * 4
+    even = core_sets(4, "even", usable=list(range(10)))
+    assert even == [[0, 1], [2, 3], [4, 5], [6, 7]]                       # disjoint, contiguous, leftovers unused
+    cpus = {0: list(range(0, 8)), 1: list(range(8, 16))}
+    numa = core_sets(4, "numa", numa_of_rank=[0, 0, 1, 1], usable=list(range(16)), node_cpus=lambda n: cpus[n])
+    assert numa == [[0, 1, 2, 3], [4, 5, 6, 7], [8, 9, 10, 11], [12, 13, 14, 15]]
+    # unknown NUMA node of some GPU -> even split; more ranks than cores -> leave affinity alone
+    assert core_sets(2, "numa", numa_of_rank=[0, None], usable=list(range(4))) == [[0, 1], [2, 3]]
+    assert core_sets(8, "even", usable=[0, 1, 2]) == [None] * 8
+
+
+def test_launcher_binds_ranks_to_disjoint_cores(tmp_path):
+    import subprocess
+    import sys
+    if len(os.sched_getaffinity(0)) < 2:
+        pytest.skip("needs two usable cores")
+    script = tmp_path / "show.py"
+    script.write_text("import os\nopen(os.environ['OUT'] + os.environ['RANK'], 'w').write(','.join(map(str, sorted(os.sched_getaffinity(0)))))\n")
+    env = dict(os.environ, OUT=str(tmp_path / "aff"))
+    res = subprocess.run([sys.executable, "-m", "distributed_llm_training_gpu_manager_b200.engine.launch", "--num_gpus=2",
+                          "--placement=linear", "--bind_cores=even", str(script), "--deepspeed_config=x"],
+                         env=env, capture_output=True, text=True, timeout=120,
+                         cwd=str(Path(__file__).resolve().parent.parent))
+    assert res.returncode == 0, res.stderr[-1500:]
+    a = set((tmp_path / "aff0").read_text().split(","))
+    b = set((tmp_path / "aff1").read_text().split(","))
+    assert a and b and not (a & b)
