@@ -16,6 +16,7 @@ preemption, ``ai_engine/spot_resiliency.py``) finishes the current step, writes 
 """
 from __future__ import annotations
 
+import gc
 import json
 import signal
 import time
@@ -46,6 +47,9 @@ class TrainerConfig:
     eval_batches: Optional[Callable[[int], Tuple]] = None    # eval_batches(k) -> (args tuple) of the k-th validation batch
     eval_every: int = 0                      # validation every N optimizer steps (0 = never)
     eval_steps: int = 1                      # validation batches per evaluation
+    gc_every: int = 0                        # > 0: Python's automatic cyclic GC is switched off for the run and a collection
+    #                                          is made every N optimizer steps instead — on every rank at the same step, so
+    #                                          the pauses coincide instead of each one stalling all ranks in turn
 
 
 @dataclass
@@ -160,6 +164,17 @@ class Trainer:
         status = "finished"
         steps_run = 0
         mf = open(c.metrics_path, "a") if (c.metrics_path and eng.rank == 0) else None
+        gc_was_on = gc.isenabled()
+        if c.gc_every > 0:
+            gc.collect()
+            gc.disable()
+        try:
+            return self._loop(eng, c, status, steps_run, mf)
+        finally:
+            if c.gc_every > 0 and gc_was_on:
+                gc.enable()
+
+    def _loop(self, eng, c, status, steps_run, mf) -> TrainResult:
         while eng.global_steps < c.total_steps:
             self.faults.at_step_start(eng)
             t_step0 = time.perf_counter()
@@ -207,6 +222,8 @@ class Trainer:
                 break
             if c.save_dir and c.save_every and eng.global_steps % c.save_every == 0:
                 self._save()
+            if c.gc_every > 0 and eng.global_steps % c.gc_every == 0:
+                gc.collect()
         ckpt.wait_for_pending_writes()
         if mf:
             mf.close()

@@ -325,3 +325,16 @@ def test_launcher_binds_ranks_to_disjoint_cores(tmp_path):
     a = set((tmp_path / "aff0").read_text().split(","))
     b = set((tmp_path / "aff1").read_text().split(","))
     assert a and b and not (a & b)
+
+
+def test_trainer_collects_garbage_on_a_common_schedule(monkeypatch):
+    import gc
+    eng = initialize(_model(), ds_dict(0), device="cpu")
+    data = synthetic_batches(VOCAB, MB, SEQ, "cpu")
+    calls, states = [], []
+    real = gc.collect
+    monkeypatch.setattr(gc, "collect", lambda *a: (calls.append(eng.global_steps), states.append(gc.isenabled()), real(*a))[2])
+    res = Trainer(eng, data, TrainerConfig(total_steps=6, gc_every=2, log_every=100)).run()
+    assert res.status == "finished" and res.final_step == 6
+    assert calls == [0, 2, 4, 6] and not any(states[1:])        # automatic GC is off while the loop runs ...
+    assert gc.isenabled()                                        # ... and back on afterwards
