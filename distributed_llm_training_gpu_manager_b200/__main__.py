@@ -48,8 +48,12 @@ def cmd_config(ns) -> Dict[str, Any]:
     from .ai_engine import DeepSpeedLauncher
     cfg = _config(ns)
     launcher = DeepSpeedLauncher()
-    return {"deepspeed_config": launcher.generate_config(cfg), "effective_batch_size": cfg.effective_batch_size,
-            "warnings": launcher.validate(cfg)}
+    ds = launcher.generate_config(cfg)
+    out = {"deepspeed_config": ds, "effective_batch_size": cfg.effective_batch_size, "warnings": launcher.validate(cfg)}
+    if getattr(ns, "explain", False):
+        from .engine.config import explain
+        out["native_engine_handling"] = explain(ds)       # key by key: honoured / fixed / not applicable, and why
+    return out
 
 
 def cmd_launch(ns) -> Dict[str, Any]:
@@ -161,6 +165,8 @@ def main(argv: List[str] = None) -> int:
         p = sub.add_parser(name)
         p.add_argument("--preset", default=None, help="7b | 13b | 70b | b200-<name>")
         p.add_argument("--set", action="append", metavar="FIELD=VALUE", help="override a DeepSpeedConfig field")
+        if name == "config":
+            p.add_argument("--explain", action="store_true", help="say, key by key, what the native engine does with it")
         if name == "launch":
             p.add_argument("--script", required=True, help="training script, or builtin:<model> for the packaged worker")
             p.add_argument("--dry-run", action="store_true")

@@ -91,6 +91,86 @@ class EngineConfig:
         return self.micro_batch * self.grad_accum * world_size
 
 
+# How the native engine treats every key the launcher can emit (ref ``deepspeed_launcher.py:124-238``).
+# "honoured" = changes what the engine does; "fixed" = the engine has one behaviour and says which; "n/a" = nothing to
+# configure in this design. ``python -m <pkg> config --explain`` prints the table for a concrete config, and
+# tests/test_round2_fixes.py fails if the launcher learns to emit a key that is missing here.
+KEY_HANDLING: Dict[str, str] = {
+    "train_micro_batch_size_per_gpu": "honoured: tokens per rank per micro-step; the native executor is built for it",
+    "gradient_accumulation_steps": "honoured: micro-steps per optimizer step; gradients accumulate in fp32 when > 1",
+    "gradient_clipping": "honoured: global-norm clipping, coefficient computed on the device (0 disables it)",
+    "steps_per_print": "honoured: caps the packaged worker's log interval",
+    "wall_clock_breakdown": "honoured: per-phase CUDA-event timers in the step metrics",
+    "dump_state": "n/a: state is inspected through engine.memory_report() and the checkpoints",
+    "communication_data_type": "honoured for fp16 compute; bf16 / fp32 compute reduce in their own dtype (an fp16 sum of "
+                               "bf16 gradients would overflow)",
+    "prescale_gradients": "honoured on the NCCL / gloo path; the fused reduce kernel sums in fp32 and scales once",
+    "gradient_predivide_factor": "honoured together with prescale_gradients",
+    "optimizer.type": "fixed: AdamW with fp32 master weights (device kernel, host C++ or NVMe-streamed)",
+    "optimizer.params.lr": "honoured", "optimizer.params.betas": "honoured", "optimizer.params.eps": "honoured",
+    "optimizer.params.weight_decay": "honoured (decoupled)",
+    "scheduler.type": "honoured: WarmupLR, WarmupDecayLR, WarmupCosineLR, constant",
+    "scheduler.params.warmup_min_lr": "honoured", "scheduler.params.warmup_max_lr": "honoured",
+    "scheduler.params.warmup_num_steps": "honoured", "scheduler.params.total_num_steps": "honoured",
+    "fp16.enabled": "honoured: fp16 compute with the dynamic loss scaler; collectives run on NCCL (the fused kernels "
+                    "reduce bf16)",
+    "fp16.loss_scale": "honoured (0 = dynamic)", "fp16.loss_scale_window": "honoured",
+    "fp16.initial_scale_power": "honoured", "fp16.hysteresis": "honoured", "fp16.min_loss_scale": "honoured",
+    "bf16.enabled": "honoured: the B200 default; enables the native kernels and the fused collectives",
+    "zero_optimization.stage": "honoured: 0 / 1 / 2 / 3",
+    "zero_optimization.allgather_partitions": "fixed: updated rows are always all-gathered (stage <= 2: pushed by the "
+                                              "optimizer kernel)",
+    "zero_optimization.allgather_bucket_size": "fixed: one unit (transformer block) per gather; audited against the size",
+    "zero_optimization.overlap_comm": "honoured: communication on a side stream, prefetch one block ahead",
+    "zero_optimization.reduce_scatter": "honoured: false = all-reduce and keep own rows (NCCL / gloo path only)",
+    "zero_optimization.reduce_bucket_size": "fixed: one unit per reduction; audited against the size",
+    "zero_optimization.contiguous_gradients": "fixed: gradients always live in flat per-unit buffers",
+    "zero_optimization.round_robin_gradients": "n/a: every tensor is row-partitioned over all ranks, so every rank owns "
+                                               "an equal share of every bucket by construction",
+    "zero_optimization.stage3_max_live_parameters": "honoured: number of gathered blocks kept resident (2 ... all)",
+    "zero_optimization.stage3_max_reuse_distance": "honoured: below one block nothing is kept beyond the pipeline's two",
+    "zero_optimization.stage3_prefetch_bucket_size": "honoured: 0 = gather on demand, > 0 = prefetch one block ahead",
+    "zero_optimization.stage3_param_persistence_threshold": "honoured: smaller tensors are replicated, not partitioned",
+    "zero_optimization.stage3_gather_16bit_weights_on_model_save": "honoured",
+    "zero_optimization.sub_group_size": "honoured: caps the tile of the host optimizer",
+    "zero_optimization.offload_optimizer.device": "honoured: none / cpu / nvme",
+    "zero_optimization.offload_optimizer.pin_memory": "honoured",
+    "zero_optimization.offload_optimizer.buffer_count": "honoured: staging slots of the NVMe tier (the cpu tier "
+                                                        "double-buffers)",
+    "zero_optimization.offload_optimizer.fast_init": "n/a: host state is initialised from the device shard in one pass",
+    "zero_optimization.offload_param.device": "honoured: cpu (nvme is served from the same pinned-host tier)",
+    "zero_optimization.offload_param.pin_memory": "honoured through offload_optimizer.pin_memory",
+    "zero_optimization.offload_param.buffer_count": "fixed: one device staging buffer per resident gathered block + root",
+    "zero_optimization.offload_param.buffer_size": "fixed: a staging buffer holds one unit's rows of the shard",
+    "zero_optimization.offload_param.max_in_cpu": "n/a: the whole 16-bit shard lives on the host (2 bytes per parameter "
+                                                  "of this rank)",
+    "activation_checkpointing.partition_activations": "n/a at tensor-parallel degree 1 (nothing to partition across)",
+    "activation_checkpointing.cpu_checkpointing": "honoured: saved activations go to pinned host memory on a side "
+                                                  "stream and come back one block ahead of backward",
+    "activation_checkpointing.contiguous_memory_optimization": "n/a: saved activations are per-block tensors",
+    "activation_checkpointing.number_checkpoints": "fixed: one checkpoint per transformer block",
+    "activation_checkpointing.synchronize_checkpoint_boundary": "n/a: ordering is by streams and events",
+    "activation_checkpointing.profile": "n/a: use wall_clock_breakdown / B200ZERO_NVTX",
+    "elasticity.enabled": "honoured: engine.schedules.elastic_batch_plan + re-partition on load at another world size",
+    "elasticity.max_train_batch_size": "honoured", "elasticity.min_train_batch_size": "honoured",
+    "elasticity.min_gpus": "honoured", "elasticity.max_gpus": "honoured", "elasticity.prefer_larger_batch_size": "honoured",
+}
+
+
+def key_paths(d: Dict[str, Any], prefix: str = ""):
+    for k, v in d.items():
+        if isinstance(v, dict):
+            yield from key_paths(v, f"{prefix}{k}.")
+        else:
+            yield f"{prefix}{k}"
+
+
+def explain(config: Dict[str, Any]) -> Dict[str, str]:
+    """key path -> how this engine treats it, for every key present in ``config``."""
+    return {p: KEY_HANDLING.get(p, "not interpreted by the native engine (kept verbatim in checkpoints)")
+            for p in key_paths(config)}
+
+
 def audit(c: EngineConfig, unit_numels=(), world_size: int = 1, fused: bool = False) -> list:
     """What this engine does with the keys of the emitted config that have no literal counterpart here
     (ref ``deepspeed_launcher.py:133-142,186-194``). Returns human-readable notes; the engine logs them once.

@@ -338,3 +338,21 @@ def test_trainer_collects_garbage_on_a_common_schedule(monkeypatch):
     assert res.status == "finished" and res.final_step == 6
     assert calls == [0, 2, 4, 6] and not any(states[1:])        # automatic GC is off while the loop runs ...
     assert gc.isenabled()                                        # ... and back on afterwards
+
+
+def test_every_key_the_launcher_can_emit_is_accounted_for():
+    from distributed_llm_training_gpu_manager_b200.ai_engine import DeepSpeedConfig, DeepSpeedLauncher
+    from distributed_llm_training_gpu_manager_b200.engine.config import KEY_HANDLING, explain, key_paths
+    L = DeepSpeedLauncher()
+    cfgs = list(L.presets().values()) + list(L.b200_presets().values()) + [
+        DeepSpeedConfig(), DeepSpeedConfig(zero_stage=0), DeepSpeedConfig(zero_stage=1, bf16_enabled=True, fp16_enabled=False),
+        DeepSpeedConfig(zero_stage=2, offload_optimizer="nvme", elastic_training=True, activation_checkpointing=False)]
+    seen = set()
+    for c in cfgs:
+        seen |= set(key_paths(L.generate_config(c)))
+    assert len(seen) >= 55
+    missing = sorted(seen - set(KEY_HANDLING))
+    assert not missing, f"emitted but not described in engine/config.py KEY_HANDLING: {missing}"
+    ex = explain(L.generate_config(DeepSpeedConfig()))
+    assert ex["zero_optimization.offload_param.device"].startswith("honoured")
+    assert all(v.split(":")[0].split()[0] in ("honoured", "fixed", "n/a") for v in ex.values())
