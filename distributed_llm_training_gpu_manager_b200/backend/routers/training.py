@@ -84,13 +84,20 @@ async def list_presets():
 
 
 @router.post("/config/generate")
-async def generate_config(request: TrainingLaunchRequest):
+async def generate_config(request: TrainingLaunchRequest, explain: bool = False):
+    """``?explain=true`` adds ``native_engine_handling``: key by key, what the built-in engine does with the emitted
+    DeepSpeed key (honoured / fixed / not applicable, and why)."""
     cfg = request.to_config()
     # build the command against a named-but-unwritten path: generating a config must not
     # leave temp files behind (the reference writes one as a side effect, ref :274-275)
     path = f"/tmp/ds_config_{cfg.model_name}.json"
-    return {"deepspeed_config": launcher.generate_config(cfg),
-            "launch_command": launcher.build_launch_command(cfg, request.training_script, request.script_args,
-                                                            config_path=path),
-            "effective_batch_size": cfg.effective_batch_size,
-            "warnings": launcher.validate(cfg)}
+    ds = launcher.generate_config(cfg)
+    out = {"deepspeed_config": ds,
+           "launch_command": launcher.build_launch_command(cfg, request.training_script, request.script_args,
+                                                           config_path=path),
+           "effective_batch_size": cfg.effective_batch_size,
+           "warnings": launcher.validate(cfg)}
+    if explain:
+        from ...engine.config import explain as _explain
+        out["native_engine_handling"] = _explain(ds)
+    return out

@@ -336,6 +336,9 @@ def test_http_surface():
     assert set(c.get("/api/v1/training/presets").json()) >= {"7b", "13b", "70b"}
     g = c.post("/api/v1/training/config/generate", json={"training_script": "t.py", "zero_stage": 2, "bf16": True}).json()
     assert g["deepspeed_config"]["zero_optimization"]["stage"] == 2 and g["effective_batch_size"] == 32
+    assert "native_engine_handling" not in g                      # same payload as the reference unless asked
+    ge = c.post("/api/v1/training/config/generate?explain=true", json={"training_script": "t.py", "zero_stage": 3}).json()
+    assert ge["native_engine_handling"]["zero_optimization.stage3_max_live_parameters"].startswith("honoured")
     assert c.post("/api/v1/monitoring/create", json={"job_id": "jj", "window_size": 20}).json()["status"] == "created"
     # NaN in, JSON out (the reference answers 500 here)
     r = c.post("/api/v1/monitoring/ingest/single", content='{"job_id":"jj","step":1,"loss":NaN}',
