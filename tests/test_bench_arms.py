@@ -48,3 +48,16 @@ def test_two_ranks_under_torchrun(impl):
     assert "fallback" not in out
     if impl == "torch":
         assert out["gpu_launches"] == 0 and "unavailable" in out["spike_to_halt_ms"]
+
+
+def test_library_arm_checkpoints_only_where_the_model_would_not_fit():
+    """Same answer on every rank (no free-memory query): Llama-3-8B with 2 x 4096 tokens needs per-block checkpointing
+    on one 180 GB GPU (fp32 master + gradient + two moments alone are 128 GB) and none from two GPUs on."""
+    sys.path.insert(0, str(ROOT))
+    from baseline.torch_zero3 import pick_checkpointing
+    from distributed_llm_training_gpu_manager_b200.models import get_config
+    c = get_config("llama3-8b")
+    hbm = 183 * 2 ** 30
+    assert pick_checkpointing(c, 1, 2, 4096, hbm) is True
+    assert pick_checkpointing(c, 2, 2, 4096, hbm) is False and pick_checkpointing(c, 8, 2, 4096, hbm) is False
+    assert pick_checkpointing(c, 1, 2, 4096, None) is False           # CPU self-test: nothing to fit into
